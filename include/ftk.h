@@ -1,0 +1,141 @@
+/*
+ * ftk.h -- C ABI of the B200 (sm_100a) training hot path of kubernetes-cloud's
+ * finetuner-workflow/finetuner: window gather, fused lm_head + cross-entropy
+ * forward/backward, data-parallel gradient all-reduce.
+ *
+ * The reference (a Python script) has no FFI of its own; each entry point
+ * below cites the reference code whose work it replaces. Paths are relative
+ * to the reference root; FT.py = finetuner-workflow/finetuner/finetuner.py.
+ *
+ * Conventions
+ *   - plain C types only; device pointers unless a parameter says "host";
+ *   - every function returns 0 on success or a negative FTK_E* code and never
+ *     throws; ftk_last_error() returns a thread-local message for the last
+ *     failure on the calling thread;
+ *   - the caller owns every buffer; the library never allocates, frees or
+ *     retains tensor memory (workspaces are caller-provided, sized by the
+ *     *_workspace queries);
+ *   - the CUDA stream is always explicit (a cudaStream_t passed as void*);
+ *     the library never synchronises it;
+ *   - the device is the one current on the calling thread;
+ *   - safe to call forward from the Python thread and backward from the
+ *     autograd engine thread (no thread-local CUDA state is kept).
+ */
+#ifndef FTK_H
+#define FTK_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FTK_ABI_VERSION 1
+
+#define FTK_OK 0
+#define FTK_EINVAL (-1)    /* bad argument (null pointer, bad shape, misalignment) */
+#define FTK_ECUDA (-2)     /* a CUDA runtime/driver call failed */
+#define FTK_EWORKSPACE (-3) /* workspace too small */
+#define FTK_ENCCL (-4)     /* NCCL missing or a NCCL call failed */
+#define FTK_EUNSUPPORTED (-5) /* not an sm_100 device / feature unavailable */
+
+/* dtype codes for ftk_lmhead_ce_bwd (dW) and ftk_dp_allreduce */
+#define FTK_BF16 0
+#define FTK_F32 1
+
+/* ABI version of the loaded library; the Python loader checks it. */
+int ftk_version(void);
+
+/* Message for the last error raised on the calling thread ("" if none). */
+const char* ftk_last_error(void);
+
+/*
+ * Window gather + label/mask construction, one launch per micro-batch.
+ * Replaces TokenizedDataset.load (FT.py:662-692: slice, uint16->int64 widen,
+ * mask rule), collector (FT.py:1030-1035: three stacks) and the label fill of
+ * ModifiedTrainer.compute_loss (FT.py:476-477: labels[~mask] = -100), plus the
+ * host->device copy of 17 B/token HF's Trainer does afterwards.
+ *
+ *   tokens      uint16 [n_ctx * T]   the token file, resident in HBM (FT.py:639-647)
+ *   ctx_idx     int64  [B]           which contexts form this batch (FT.py:757-772 ordering)
+ *   pad_id      tokenizer.pad_token_id; pad_is_eos = (pad_id == eos_id) (FT.py:650-651)
+ *   shift_labels 0: labels[b,t] = mask ? ids[b,t] : -100   (what the reference hands to HF)
+ *               1: labels[b,t] = (t+1<T && mask[b,t+1]) ? ids[b,t+1] : -100
+ *                  (HF's causal shift, transformers loss_utils.ForCausalLMLoss, folded in:
+ *                  the targets the fused loss consumes)
+ *   input_ids   int64 [B,T]; labels int64 [B,T]; mask uint8 [B,T] (0/1, torch.bool layout)
+ *   n_valid     int32 [B] or NULL: number of labels != -100 per row
+ * Every ctx_idx[b] must lie in [0, n_ctx); the index list lives on the device
+ * and is not validated here (the host-side dataset class validates it).
+ * T % 16 == 0 and 16-byte aligned buffers take the vectorised path; other
+ * shapes take a scalar path with the same results.
+ */
+int ftk_gather_windows(const uint16_t* tokens, int64_t n_ctx, int32_t T, const int64_t* ctx_idx, int32_t B,
+                       int32_t pad_id, int32_t pad_is_eos, int32_t shift_labels, int64_t* input_ids, int64_t* labels,
+                       uint8_t* mask, int32_t* n_valid, void* stream);
+
+/*
+ * Fused lm_head projection + causal-LM cross-entropy, forward.
+ * Replaces logits = lm_head(hidden) (HF modeling_gpt_neo.py lm_head, reached
+ * from FT.py:479 super().compute_loss -> model(**inputs)) followed by
+ * logits.float() + cross_entropy(ignore_index=-100, reduction=mean)
+ * (transformers loss_utils.py fixed_cross_entropy / ForCausalLMLoss).
+ * The [M,V] logits never exist in HBM.
+ *
+ *   H        bf16 [M,d] row-major (hidden states at the lm_head input)
+ *   W        bf16 [V,d] row-major (lm_head.weight; tied to wte.weight for GPT-2/GPT-Neo)
+ *   bias     bf16 [V] or NULL (GPT-J has one)
+ *   targets  int64 [M], already shifted; -100 = ignore
+ *   lse      fp32 [M] out: log-sum-exp of each row's logits (saved for backward)
+ *   loss_sum fp32 [1] out: sum over valid rows of (lse - logit[target])
+ *   n_valid  int32 [1] out: number of rows with target != -100
+ *            (mean loss = loss_sum / n_valid; NaN when n_valid == 0, as in the reference)
+ * Requirements: d % 64 == 0, H/W 16-byte aligned.
+ */
+size_t ftk_lmhead_ce_fwd_workspace(int64_t M, int32_t d, int32_t V);
+int ftk_lmhead_ce_fwd(const void* H, const void* W, const void* bias, const int64_t* targets, int64_t M, int32_t d,
+                      int32_t V, float* lse, float* loss_sum, int32_t* n_valid, void* workspace,
+                      size_t workspace_bytes, void* stream);
+
+/*
+ * Fused backward of the above (autograd of lm_head + cross_entropy in the
+ * reference, reached from loss.backward() inside HF Trainer.training_step).
+ *   dZ = (softmax(z) - onehot(target)) * scale for valid rows, 0 for ignored,
+ *   scale = grad_scale * (grad_scale_dev ? *grad_scale_dev : 1) / (n_valid_dev ? *n_valid_dev : 1)
+ *   dH = dZ . W          bf16 [M,d]
+ *   dW (+)= dZ^T . H     [V,d], dw_dtype FTK_BF16 or FTK_F32; accumulate != 0 adds into dW
+ *                        (tied embeddings, gradient accumulation)
+ *   dbias (+)= sum_m dZ  fp32 [V] or NULL
+ * The logits are recomputed tile by tile from H, W and lse; dZ passes through
+ * the workspace as bf16 in row slabs. slab_rows = 0 picks the default.
+ */
+size_t ftk_lmhead_ce_bwd_workspace(int64_t M, int32_t d, int32_t V, int64_t slab_rows);
+int ftk_lmhead_ce_bwd(const void* H, const void* W, const void* bias, const int64_t* targets, const float* lse,
+                      int64_t M, int32_t d, int32_t V, float grad_scale, const float* grad_scale_dev,
+                      const int32_t* n_valid_dev, void* dH, void* dW, int32_t dw_dtype, int32_t accumulate,
+                      float* dbias, void* workspace, size_t workspace_bytes, void* stream);
+
+/*
+ * Data-parallel gradient all-reduce (replaces DeepSpeed ZeRO's bucketed
+ * gradient reduction configured by finetuner/ds_config.json:27-45 and enabled
+ * at FT.py:911-923). One communicator + one high-priority comm stream per rank.
+ *   ftk_dp_unique_id  host: fills 128 bytes with an ncclUniqueId (rank 0 calls it, then
+ *                     ships the bytes to the other ranks by any means)
+ *   ftk_dp_init       host id bytes, rank, world -> opaque handle
+ *   ftk_dp_allreduce  on the comm stream: wait for `ready_stream` work issued so far,
+ *                     multiply by prescale (1/world for the reference's mean), ncclAllReduce(sum)
+ *                     in place over `count` elements of dtype (FTK_BF16/FTK_F32); never blocks the host
+ *   ftk_dp_join       makes `stream` wait for everything issued on the comm stream so far
+ */
+typedef struct ftk_dp ftk_dp_t;
+int ftk_dp_unique_id(void* id128_host);
+int ftk_dp_init(const void* id128_host, int32_t rank, int32_t world, ftk_dp_t** out);
+int ftk_dp_allreduce(ftk_dp_t* dp, void* buf, size_t count, int32_t dtype, float prescale, void* ready_stream);
+int ftk_dp_join(ftk_dp_t* dp, void* stream);
+int ftk_dp_destroy(ftk_dp_t* dp);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FTK_H */

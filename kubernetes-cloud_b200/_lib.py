@@ -1,0 +1,79 @@
+"""ctypes binding of the C ABI declared in include/ftk.h (lib/libftk.so).
+
+There is no fallback: if the library is missing or its ABI version differs, importing an op raises.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import subprocess
+from ctypes import POINTER, c_char_p, c_float, c_int32, c_int64, c_size_t, c_void_p
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "lib", "libftk.so")
+CSRC = os.path.join(_PKG, "csrc")
+ABI_VERSION = 1
+
+FTK_BF16, FTK_F32 = 0, 1
+
+# name -> (restype, argtypes); mirrors include/ftk.h one to one
+SIGNATURES = {
+    "ftk_version": (c_int32, []),
+    "ftk_last_error": (c_char_p, []),
+    "ftk_gather_windows": (c_int32, [c_void_p, c_int64, c_int32, c_void_p, c_int32, c_int32, c_int32, c_int32,
+                                     c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "ftk_lmhead_ce_fwd_workspace": (c_size_t, [c_int64, c_int32, c_int32]),
+    "ftk_lmhead_ce_fwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p,
+                                    c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "ftk_lmhead_ce_bwd_workspace": (c_size_t, [c_int64, c_int32, c_int32, c_int64]),
+    "ftk_lmhead_ce_bwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32,
+                                    c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_void_p,
+                                    c_void_p, c_size_t, c_void_p]),
+    "ftk_dp_unique_id": (c_int32, [c_void_p]),
+    "ftk_dp_init": (c_int32, [c_void_p, c_int32, c_int32, POINTER(c_void_p)]),
+    "ftk_dp_allreduce": (c_int32, [c_void_p, c_void_p, c_size_t, c_int32, c_float, c_void_p]),
+    "ftk_dp_join": (c_int32, [c_void_p, c_void_p]),
+    "ftk_dp_destroy": (c_int32, [c_void_p]),
+}
+
+
+class FtkError(RuntimeError):
+    pass
+
+
+def build(verbose: bool = False) -> str:
+    """Compile csrc/*.cu for sm_100a into lib/libftk.so (nvcc cross-compiles without a GPU)."""
+    res = subprocess.run(["make", "-C", CSRC, "-j4"], capture_output=True, text=True)
+    if verbose or res.returncode != 0:
+        print(res.stdout)
+        print(res.stderr)
+    if res.returncode != 0:
+        raise FtkError("building libftk.so failed")
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib() -> ctypes.CDLL:
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise FtkError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(there is no CPU or eager fallback)")
+        l = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(l, name)  # AttributeError if the .so lacks a declared symbol
+            fn.restype = res
+            fn.argtypes = args
+        v = l.ftk_version()
+        if v != ABI_VERSION:
+            raise FtkError(f"libftk.so ABI version {v}, binding expects {ABI_VERSION}: rebuild the library")
+        _lib = l
+    return _lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = lib().ftk_last_error()
+        raise FtkError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")

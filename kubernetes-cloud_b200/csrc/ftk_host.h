@@ -1,0 +1,41 @@
+// Host-side helpers shared by the C-ABI translation units: thread-local error text, CUDA checks.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+
+#include "../../include/ftk.h"
+
+namespace ftk {
+
+char* err_buf();  // thread-local, 512 bytes (defined in api.cu)
+
+inline int fail(int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(err_buf(), 512, fmt, ap);
+  va_end(ap);
+  return code;
+}
+
+#define FTK_CUDA_CHECK(expr)                                                                              \
+  do {                                                                                                    \
+    cudaError_t e__ = (expr);                                                                             \
+    if (e__ != cudaSuccess)                                                                               \
+      return ::ftk::fail(FTK_ECUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), __FILE__, __LINE__); \
+  } while (0)
+
+#define FTK_REQUIRE(cond, ...)                              \
+  do {                                                      \
+    if (!(cond)) return ::ftk::fail(FTK_EINVAL, __VA_ARGS__); \
+  } while (0)
+
+// Cached per-device facts (SM count, compute capability).
+struct DeviceInfo {
+  int sm_count;
+  int cc_major;
+  int cc_minor;
+};
+int get_device_info(DeviceInfo* out);  // current device; FTK_OK or error
+
+}  // namespace ftk

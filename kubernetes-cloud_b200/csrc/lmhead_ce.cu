@@ -1,0 +1,931 @@
+// G2/G3: fused lm_head projection + cross-entropy for sm_100a.
+//
+// One warp-specialised tcgen05 kernel template (TMA -> shared memory -> tcgen05.mma -> TMEM -> epilogue warps)
+// is instantiated four times:
+//   fwd   S = H.W^T, online-softmax epilogue: per-row running max / sum-exp / target logit; no logits in HBM
+//   dz    S recomputed, epilogue forms dZ = (exp(S - lse) - onehot) * scale in bf16 into the slab workspace
+//   dH    dH = dZ . W        (A K-major, B MN-major)
+//   dW    dW (+)= dZ^T . H   (A MN-major, B MN-major)
+// Reference arithmetic being replaced: HF lm_head Linear + loss_utils.ForCausalLMLoss and their autograd,
+// reached from FT.py:479 (see include/ftk.h).
+//
+// Warp roles per CTA (256 threads): warp 0 = TMA producer (one lane), warp 1 = MMA issuer (one lane, leader CTA
+// of a pair only), warp 2 = TMEM allocator, warps 4-7 = epilogue (one accumulator row per thread).
+// Three mbarrier pipelines: smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue).
+#include <cuda.h>
+#include <math.h>
+#include <stdlib.h>
+
+#include "ftk_host.h"
+#include "ftk_ptx.cuh"
+
+namespace {
+using namespace ftk;
+
+constexpr int BM = 128;  // accumulator rows per CTA (= TMEM lanes)
+constexpr int BK = 64;   // K elements per smem stage: one 128-byte swizzle atom of bf16
+constexpr int UK = 16;   // K per tcgen05.mma (bf16)
+constexpr int kThreads = 256;
+constexpr int kAccStages = 2;
+constexpr int kTmemCols = 512;
+constexpr float kLog2e = 1.4426950408889634f;
+constexpr float kLn2 = 0.6931471805599453f;
+constexpr int kMaxChunks = 32;  // upper bound on vocabulary chunks (sizes the forward workspace)
+
+// Work decomposition. A unit is (m block, chunk of consecutive N tiles); units are dealt round-robin to CTAs
+// (or CTA pairs). Consecutive unit ids share the outer index, so CTAs running at the same time share operand
+// tiles in L2.
+struct Sched {
+  int n_units;
+  int n_inner;          // units per outer index
+  int inner_is_m;       // 1: unit -> (chunk = outer, m_blk = inner); 0: (m_blk = outer, chunk = inner)
+  int tiles_per_chunk;  // N tiles per unit
+  int n_ntile;          // N tiles in total
+  int n_kblk;           // K blocks of BK
+};
+
+__device__ __forceinline__ void decode_unit(const Sched& sc, int u, int& m_blk, int& chunk) {
+  const int outer = u / sc.n_inner, inner = u - outer * sc.n_inner;
+  m_blk = sc.inner_is_m ? inner : outer;
+  chunk = sc.inner_is_m ? outer : inner;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+
+// ------------------------------------------------------------------------------------------------ epilogues
+// Each epilogue thread owns one accumulator row. tile() reads the BN fp32 columns of that row from TMEM in
+// groups of 32 and must finish all TMEM loads before returning (the caller then frees the accumulator stage).
+
+// Forward: online softmax statistics over this unit's vocabulary chunk.
+struct FwdEpi {
+  struct Params {
+    const int64_t* targets;     // [M]
+    const __nv_bfloat16* bias;  // [V] or null
+    float* pmax;                // [n_chunks][Mpad] running max (natural units)
+    float* psum;                // [n_chunks][Mpad] sum exp(z - max)
+    float* ztgt;                // [Mpad] logit at the target column
+    int M, V, Mpad;
+  };
+  struct State {
+    float m, s, zt;
+    int tgt, row, chunk;
+    bool has;
+  };
+  template <int BN>
+  static __device__ __forceinline__ void begin_unit(State& st, const Params& p, int row, int chunk) {
+    st.row = row;
+    st.chunk = chunk;
+    st.m = -INFINITY;
+    st.s = 0.f;
+    st.zt = 0.f;
+    st.has = false;
+    st.tgt = (row < p.M) ? static_cast<int>(p.targets[row]) : -1;
+  }
+  template <int BN>
+  static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0) {
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      const int col0 = n0 + c * 32;
+      if (col0 >= p.V) break;  // warp-uniform
+      float v[32];
+      tmem_ld32(taddr + c * 32, v);
+      tmem_ld_wait();
+      if (p.bias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < p.V) v[j] += __bfloat162float(__ldg(p.bias + col0 + j));
+      }
+      if (col0 + 32 > p.V) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j >= p.V) v[j] = -INFINITY;  // TMA zero-fills phantom rows of W: mask, do not count
+      }
+      if (st.tgt >= col0 && st.tgt < col0 + 32) {
+        const int jj = st.tgt - col0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j == jj) st.zt = v[j];
+        st.has = true;
+      }
+      float cmax = v[0];
+#pragma unroll
+      for (int j = 1; j < 32; ++j) cmax = fmaxf(cmax, v[j]);
+      const float m_new = fmaxf(st.m, cmax);  // finite: column col0 < V is real
+      const float neg = -m_new * kLog2e;
+      float acc = 0.f;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) acc += exp2f(fmaf(v[j], kLog2e, neg));
+      st.s = st.s * exp2f(fmaf(st.m, kLog2e, neg)) + acc;  // exp2(-inf) = 0 on the first group
+      st.m = m_new;
+    }
+  }
+  template <int BN>
+  static __device__ __forceinline__ void end_unit(State& st, const Params& p) {
+    if (st.row < p.M) {
+      p.pmax[static_cast<size_t>(st.chunk) * p.Mpad + st.row] = st.m;
+      p.psum[static_cast<size_t>(st.chunk) * p.Mpad + st.row] = st.s;
+      if (st.has) p.ztgt[st.row] = st.zt;
+    }
+  }
+};
+
+// Backward stage 1: dZ tile from the recomputed logits.
+struct DzEpi {
+  struct Params {
+    const int64_t* targets;     // [rows] (slab-relative)
+    const __nv_bfloat16* bias;  // [V] or null
+    const float* lse;           // [rows]
+    __nv_bfloat16* dz;          // [rows][ld]
+    const float* scale_dev;     // optional device scalar multiplied into scale
+    const int32_t* nvalid_dev;  // optional device count divided out of scale
+    float scale;
+    int rows, V, ld;
+  };
+  struct State {
+    float l2, sc;
+    int tgt, row;
+  };
+  template <int BN>
+  static __device__ __forceinline__ void begin_unit(State& st, const Params& p, int row, int) {
+    st.row = row;
+    st.tgt = -1;
+    st.l2 = 0.f;
+    st.sc = 0.f;
+    if (row < p.rows) {
+      st.tgt = static_cast<int>(p.targets[row]);
+      st.l2 = -p.lse[row] * kLog2e;
+      float sc = p.scale;
+      if (p.scale_dev != nullptr) sc *= __ldg(p.scale_dev);
+      if (p.nvalid_dev != nullptr) sc /= static_cast<float>(__ldg(p.nvalid_dev));
+      st.sc = (st.tgt >= 0) ? sc : 0.f;  // ignored rows contribute no gradient
+    }
+  }
+  template <int BN>
+  static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0) {
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      const int col0 = n0 + c * 32;
+      if (col0 >= p.ld) break;  // warp-uniform
+      float v[32];
+      tmem_ld32(taddr + c * 32, v);
+      tmem_ld_wait();
+      if (p.bias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < p.V) v[j] += __bfloat162float(__ldg(p.bias + col0 + j));
+      }
+      uint32_t w[16];
+#pragma unroll
+      for (int j = 0; j < 32; j += 2) {
+        float g0 = exp2f(fmaf(v[j], kLog2e, st.l2));
+        float g1 = exp2f(fmaf(v[j + 1], kLog2e, st.l2));
+        g0 = (col0 + j == st.tgt) ? g0 - 1.f : g0;
+        g1 = (col0 + j + 1 == st.tgt) ? g1 - 1.f : g1;
+        g0 = (col0 + j < p.V) ? g0 * st.sc : 0.f;
+        g1 = (col0 + j + 1 < p.V) ? g1 * st.sc : 0.f;
+        w[j >> 1] = pack_bf16x2(g0, g1);
+      }
+      if (st.row < p.rows) {
+        uint4* dst = reinterpret_cast<uint4*>(p.dz + static_cast<size_t>(st.row) * p.ld + col0);
+#pragma unroll
+        for (int q = 0; q < 4; ++q)
+          if (col0 + q * 8 < p.ld) dst[q] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+      }
+    }
+  }
+  template <int BN>
+  static __device__ __forceinline__ void end_unit(State&, const Params&) {}
+};
+
+// Plain GEMM epilogue: out[row, col] (+)= acc, bf16 or fp32 row-major.
+template <bool kF32>
+struct StoreEpi {
+  struct Params {
+    void* out;
+    int rows, cols, ld, accumulate;
+  };
+  struct State {
+    int row;
+  };
+  template <int BN>
+  static __device__ __forceinline__ void begin_unit(State& st, const Params&, int row, int) {
+    st.row = row;
+  }
+  template <int BN>
+  static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0) {
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      const int col0 = n0 + c * 32;
+      if (col0 >= p.cols) break;  // warp-uniform
+      float v[32];
+      tmem_ld32(taddr + c * 32, v);
+      tmem_ld_wait();
+      if (st.row >= p.rows) {
+        // rows past the end: nothing to store (no `continue`: the next tcgen05.ld needs a converged warp)
+      } else if constexpr (kF32) {
+        float4* dst = reinterpret_cast<float4*>(static_cast<float*>(p.out) + static_cast<size_t>(st.row) * p.ld + col0);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) {
+          if (col0 + q * 4 >= p.cols) break;
+          float4 o = make_float4(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);
+          if (p.accumulate) {
+            const float4 old = dst[q];
+            o.x += old.x;
+            o.y += old.y;
+            o.z += old.z;
+            o.w += old.w;
+          }
+          dst[q] = o;
+        }
+      } else {
+        uint4* dst = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + static_cast<size_t>(st.row) * p.ld +
+                                              col0);
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if (col0 + q * 8 >= p.cols) break;
+          float* x = v + 8 * q;
+          if (p.accumulate) {
+            const uint4 old = dst[q];
+            const uint32_t ow[4] = {old.x, old.y, old.z, old.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&ow[e]);
+              x[2 * e] += __low2float(h);
+              x[2 * e + 1] += __high2float(h);
+            }
+          }
+          dst[q] = make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]), pack_bf16x2(x[4], x[5]),
+                              pack_bf16x2(x[6], x[7]));
+        }
+      }
+    }
+  }
+  template <int BN>
+  static __device__ __forceinline__ void end_unit(State&, const Params&) {}
+};
+
+// ------------------------------------------------------------------------------------------------ the kernel
+template <int kCG, int BN, int kStages>
+struct SmemLayout {
+  static constexpr int LOAD_BN = BN / kCG;
+  static constexpr uint32_t A_BYTES = BM * BK * 2;
+  static constexpr uint32_t B_BYTES = LOAD_BN * BK * 2;
+  static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr uint32_t BAR_OFF = kStages * STAGE_BYTES;
+  static constexpr uint32_t BYTES = 1024 /*alignment slack*/ + BAR_OFF + (2 * kStages + 2 * kAccStages) * 8 + 16;
+};
+
+template <int kCG, int BN, int kStages, bool kAMN, bool kBMN, class Epi>
+__global__ void __launch_bounds__(kThreads, 1)
+    umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Sched sc,
+                const typename Epi::Params ep) {
+  using L = SmemLayout<kCG, BN, kStages>;
+  constexpr int LOAD_BN = L::LOAD_BN;
+  static_assert(BN % 32 == 0 && BN <= 256 && kAccStages * BN <= kTmemCols, "accumulator does not fit TMEM");
+  static_assert(LOAD_BN % 64 == 0, "B tile must be whole 64-wide swizzle atoms");
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = smem + kStages * L::A_BYTES;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
+  uint64_t* empty = full + kStages;
+  uint64_t* tfull = empty + kStages;
+  uint64_t* tempty = tfull + kAccStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + kAccStages);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t rank = (kCG == 2) ? cluster_ctarank() : 0u;
+  const int cl = blockIdx.x / kCG, n_cl = gridDim.x / kCG;
+
+  if constexpr (kCG == 2) cluster_sync_all();  // both CTAs resident before the paired TMEM allocation
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(&full[i], kCG);  // leader: own arrive.expect_tx + the peer's arrive
+      mbar_init(&empty[i], 1);   // tcgen05.commit (multicast to both CTAs of a pair)
+    }
+    for (int i = 0; i < kAccStages; ++i) {
+      mbar_init(&tfull[i], 1);         // tcgen05.commit
+      mbar_init(&tempty[i], kCG * 4);  // one arrive per epilogue warp of each CTA
+    }
+    fence_mbar_init();
+  }
+  if (warp == 2) {
+    tmem_alloc<kCG>(tmem_slot, kTmemCols);
+    tmem_relinquish<kCG>();
+  }
+  tc_fence_before();
+  if constexpr (kCG == 2)
+    cluster_sync_all();
+  else
+    __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ============================== TMA producer ==============================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int u = cl; u < sc.n_units; u += n_cl) {
+        int m_blk, chunk;
+        decode_unit(sc, u, m_blk, chunk);
+        const int m0 = (m_blk * kCG + static_cast<int>(rank)) * BM;
+        const int nt_begin = chunk * sc.tiles_per_chunk;
+        const int nt_end = min(nt_begin + sc.tiles_per_chunk, sc.n_ntile);
+        for (int nt = nt_begin; nt < nt_end; ++nt) {
+          const int n0 = nt * BN + static_cast<int>(rank) * LOAD_BN;
+          for (int kb = 0; kb < sc.n_kblk; ++kb) {
+            mbar_wait(&empty[stage], phase ^ 1);
+            uint64_t* bar = &full[stage];
+            if constexpr (kCG == 1) {
+              mbar_arrive_expect_tx(bar, L::STAGE_BYTES);
+            } else {
+              if (rank == 0)
+                mbar_arrive_expect_tx(bar, 2 * L::STAGE_BYTES);
+              else
+                mbar_arrive_cluster(bar, 0);
+            }
+            uint8_t* a_dst = sA + stage * L::A_BYTES;
+            uint8_t* b_dst = sB + stage * L::B_BYTES;
+            const int k0 = kb * BK;
+            if constexpr (!kAMN) {
+              if constexpr (kCG == 1)
+                tma_load_2d(a_dst, &tmA, bar, k0, m0);
+              else
+                tma_load_2d_pair(a_dst, &tmA, bar, k0, m0);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BM / 64; ++j) {
+                if constexpr (kCG == 1)
+                  tma_load_2d(a_dst + j * (BK * 128), &tmA, bar, m0 + 64 * j, k0);
+                else
+                  tma_load_2d_pair(a_dst + j * (BK * 128), &tmA, bar, m0 + 64 * j, k0);
+              }
+            }
+            if constexpr (!kBMN) {
+              if constexpr (kCG == 1)
+                tma_load_2d(b_dst, &tmB, bar, k0, n0);
+              else
+                tma_load_2d_pair(b_dst, &tmB, bar, k0, n0);
+            } else {
+#pragma unroll
+              for (int j = 0; j < LOAD_BN / 64; ++j) {
+                if constexpr (kCG == 1)
+                  tma_load_2d(b_dst + j * (BK * 128), &tmB, bar, n0 + 64 * j, k0);
+                else
+                  tma_load_2d_pair(b_dst + j * (BK * 128), &tmB, bar, n0 + 64 * j, k0);
+              }
+            }
+            if (++stage == kStages) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ============================== MMA issuer (leader CTA) ==============================
+    if (lane == 0 && rank == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM * kCG, BN, kAMN, kBMN);
+      // K-major operand: rows of 128 B, 8-row groups 1024 B apart (SBO); LBO unused.
+      // MN-major operand: 64-element (128 B) runs along MN, 8 k-rows per 1024 B group (SBO), next 64 MN
+      // elements one whole [BK x 128 B] box further (LBO).
+      constexpr uint32_t kLboMN = BK * 128, kSbo = 1024;
+      constexpr uint32_t a_kstep = kAMN ? (UK * 128) : (UK * 2);
+      constexpr uint32_t b_kstep = kBMN ? (UK * 128) : (UK * 2);
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t it = 0;
+      for (int u = cl; u < sc.n_units; u += n_cl) {
+        int m_blk, chunk;
+        decode_unit(sc, u, m_blk, chunk);
+        const int nt_begin = chunk * sc.tiles_per_chunk;
+        const int nt_end = min(nt_begin + sc.tiles_per_chunk, sc.n_ntile);
+        for (int nt = nt_begin; nt < nt_end; ++nt, ++it) {
+          const uint32_t as = it & 1, aphase = (it >> 1) & 1;
+          mbar_wait(&tempty[as], aphase ^ 1);
+          tc_fence_after();
+          const uint32_t tmem_d = tmem_base + as * BN;
+          for (int kb = 0; kb < sc.n_kblk; ++kb) {
+            mbar_wait(&full[stage], phase);
+            tc_fence_after();
+            const uint32_t a_addr = smem_u32(sA + stage * L::A_BYTES);
+            const uint32_t b_addr = smem_u32(sB + stage * L::B_BYTES);
+#pragma unroll
+            for (int k = 0; k < BK / UK; ++k) {
+              const uint64_t adesc = make_sw128_desc(a_addr + k * a_kstep, kAMN ? kLboMN : 0u, kSbo);
+              const uint64_t bdesc = make_sw128_desc(b_addr + k * b_kstep, kBMN ? kLboMN : 0u, kSbo);
+              umma_bf16<kCG>(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+            umma_commit<kCG>(&empty[stage]);  // frees the smem stage once these MMAs have read it
+            if (kb == sc.n_kblk - 1) umma_commit<kCG>(&tfull[as]);
+            if (++stage == kStages) {
+              stage = 0;
+              phase ^= 1;
+            }
+          }
+        }
+      }
+    }
+  } else if (warp >= 4) {
+    // ============================== epilogue ==============================
+    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int row_in_tile = q * 32 + lane;
+    typename Epi::State st;
+    uint32_t it = 0;
+    for (int u = cl; u < sc.n_units; u += n_cl) {
+      int m_blk, chunk;
+      decode_unit(sc, u, m_blk, chunk);
+      const int row = (m_blk * kCG + static_cast<int>(rank)) * BM + row_in_tile;
+      Epi::template begin_unit<BN>(st, ep, row, chunk);
+      const int nt_begin = chunk * sc.tiles_per_chunk;
+      const int nt_end = min(nt_begin + sc.tiles_per_chunk, sc.n_ntile);
+      for (int nt = nt_begin; nt < nt_end; ++nt, ++it) {
+        const uint32_t as = it & 1, aphase = (it >> 1) & 1;
+        mbar_wait(&tfull[as], aphase);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
+        Epi::template tile<BN>(st, ep, taddr, nt * BN);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if constexpr (kCG == 1)
+            mbar_arrive(&tempty[as]);
+          else
+            mbar_arrive_cluster(&tempty[as], 0);
+        }
+      }
+      Epi::template end_unit<BN>(st, ep);
+    }
+  }
+
+  // ---- teardown: nobody may leave while a peer can still touch its smem / barriers / TMEM
+  __syncwarp();
+  tc_fence_before();
+  if constexpr (kCG == 2)
+    cluster_sync_all();
+  else
+    __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc<kCG>(tmem_base, kTmemCols);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ small kernels
+// Merge the per-chunk softmax statistics: lse per row, then a deterministic two-level reduction of the loss.
+__global__ void __launch_bounds__(256) fwd_finalize_kernel(const float* __restrict__ pmax,
+                                                           const float* __restrict__ psum,
+                                                           const float* __restrict__ ztgt,
+                                                           const int64_t* __restrict__ targets, int M, int Mpad,
+                                                           int n_chunks, float* __restrict__ lse,
+                                                           float* __restrict__ blk_loss, int* __restrict__ blk_cnt,
+                                                           unsigned int* __restrict__ ticket,
+                                                           float* __restrict__ loss_sum, int* __restrict__ n_valid) {
+  __shared__ float s_loss[8];
+  __shared__ int s_cnt[8];
+  __shared__ bool s_last;
+  const int tid = threadIdx.x;
+  const int row = blockIdx.x * 256 + tid;
+  float loss = 0.f;
+  int cnt = 0;
+  if (row < M) {
+    float gm = -INFINITY;
+    for (int c = 0; c < n_chunks; ++c) gm = fmaxf(gm, pmax[static_cast<size_t>(c) * Mpad + row]);
+    float s = 0.f;
+    for (int c = 0; c < n_chunks; ++c) {
+      const size_t o = static_cast<size_t>(c) * Mpad + row;
+      s += psum[o] * exp2f((pmax[o] - gm) * kLog2e);
+    }
+    const float l = gm + log2f(s) * kLn2;
+    lse[row] = l;
+    if (targets[row] >= 0) {
+      loss = l - ztgt[row];
+      cnt = 1;
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    loss += __shfl_xor_sync(0xffffffffu, loss, o);
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  }
+  if ((tid & 31) == 0) {
+    s_loss[tid >> 5] = loss;
+    s_cnt[tid >> 5] = cnt;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    float bl = 0.f;
+    int bc = 0;
+    for (int w = 0; w < 8; ++w) {
+      bl += s_loss[w];
+      bc += s_cnt[w];
+    }
+    blk_loss[blockIdx.x] = bl;
+    blk_cnt[blockIdx.x] = bc;
+    __threadfence();
+    const unsigned int t = atomicAdd(ticket, 1u);
+    s_last = (t == gridDim.x - 1);
+  }
+  __syncthreads();
+  if (s_last && tid == 0) {  // last block to finish: fixed-order sum of the block partials
+    __threadfence();
+    double tl = 0.0;
+    int tc = 0;
+    for (unsigned int b = 0; b < gridDim.x; ++b) {
+      tl += static_cast<double>(reinterpret_cast<volatile float*>(blk_loss)[b]);
+      tc += reinterpret_cast<volatile int*>(blk_cnt)[b];
+    }
+    *loss_sum = static_cast<float>(tl);
+    *n_valid = tc;
+    *ticket = 0u;
+  }
+}
+
+// dbias[v] += sum over slab rows of dZ[row, v].
+__global__ void __launch_bounds__(128) dbias_kernel(const __nv_bfloat16* __restrict__ dz, int rows, int V, int ld,
+                                                    int rows_per_block, float* __restrict__ dbias) {
+  const int col = (blockIdx.x * 128 + threadIdx.x) * 2;
+  if (col >= V) return;
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(rows, r0 + rows_per_block);
+  float a0 = 0.f, a1 = 0.f;
+  for (int r = r0; r < r1; ++r) {
+    const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(dz + static_cast<size_t>(r) * ld + col);
+    a0 += __low2float(h);
+    a1 += __high2float(h);
+  }
+  atomicAdd(dbias + col, a0);
+  if (col + 1 < V) atomicAdd(dbias + col + 1, a1);
+}
+
+// ------------------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int get_encode_fn(EncodeTiledFn* out) {
+  static EncodeTiledFn cached = nullptr;
+  if (cached == nullptr) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    FTK_CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    if (qres != cudaDriverEntryPointSuccess || fn == nullptr)
+      return fail(FTK_EUNSUPPORTED, "cuTensorMapEncodeTiled not available from the driver");
+    cached = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  *out = cached;
+  return FTK_OK;
+}
+
+// bf16 row-major [dim1][dim0] with row pitch pitch_bytes; box = box0 x box1 elements; 128-byte swizzle.
+// Out-of-bounds parts of a box are filled with zeros.
+int make_tmap(CUtensorMap* tm, const void* base, uint64_t dim0, uint64_t dim1, uint64_t pitch_bytes, uint32_t box0,
+              uint32_t box1) {
+  EncodeTiledFn enc = nullptr;
+  if (int rc = get_encode_fn(&enc)) return rc;
+  FTK_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "tensor base %p is not 16-byte aligned", base);
+  FTK_REQUIRE(pitch_bytes % 16 == 0, "row pitch %llu is not a multiple of 16 bytes",
+              static_cast<unsigned long long>(pitch_bytes));
+  FTK_REQUIRE(box0 * 2 <= 128 && box1 <= 256, "bad TMA box %u x %u", box0, box1);
+  const cuuint64_t dims[2] = {dim0, dim1};
+  const cuuint64_t strides[1] = {pitch_bytes};
+  const cuuint32_t box[2] = {box0, box1};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(FTK_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
+  return FTK_OK;
+}
+
+template <int kCG, int BN, int kStages, bool kAMN, bool kBMN, class Epi>
+int launch_umma(const CUtensorMap& tmA, const CUtensorMap& tmB, const Sched& sc, const typename Epi::Params& ep,
+                int sm_count, cudaStream_t st) {
+  using L = SmemLayout<kCG, BN, kStages>;
+  auto kern = umma_kernel<kCG, BN, kStages, kAMN, kBMN, Epi>;
+  static bool attr_done[64] = {false};  // per instantiation and device
+  int dev = 0;
+  FTK_CUDA_CHECK(cudaGetDevice(&dev));
+  if (!attr_done[dev & 63]) {
+    FTK_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(L::BYTES)));
+    attr_done[dev & 63] = true;
+  }
+  int n_cl = sm_count / kCG;
+  if (n_cl > sc.n_units) n_cl = sc.n_units;
+  if (n_cl <= 0) return FTK_OK;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(static_cast<unsigned>(n_cl * kCG));
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = L::BYTES;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = kCG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  FTK_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tmA, tmB, sc, ep));
+  return FTK_OK;
+}
+
+// Which CTA grouping to use: 2 (CTA pairs, 256-row tiles) unless FTK_CTA_GROUP=1 is set in the environment.
+int cta_group() {
+  const char* e = getenv("FTK_CTA_GROUP");
+  return (e != nullptr && atoi(e) == 1) ? 1 : 2;
+}
+
+inline int ceil_div(int64_t a, int64_t b) { return static_cast<int>((a + b - 1) / b); }
+inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
+
+// Split the vocabulary sweep of each m block into chunks so the (m block x chunk) units fill the machine evenly.
+void plan_chunks(int n_mblk, int n_ntile, int n_groups, int* n_chunks, int* tiles_per_chunk) {
+  int best_s = 1;
+  int64_t best_cost = INT64_MAX;
+  const int s_max = n_ntile < kMaxChunks ? n_ntile : kMaxChunks;
+  for (int s = 1; s <= s_max; ++s) {
+    const int tpc = ceil_div(n_ntile, s);
+    const int s_eff = ceil_div(n_ntile, tpc);
+    const int64_t units = static_cast<int64_t>(n_mblk) * s_eff;
+    const int64_t cost = ((units + n_groups - 1) / n_groups) * tpc;
+    if (cost < best_cost) {
+      best_cost = cost;
+      best_s = s_eff;
+    }
+  }
+  *n_chunks = best_s;
+  *tiles_per_chunk = ceil_div(n_ntile, best_s);
+  *n_chunks = ceil_div(n_ntile, *tiles_per_chunk);
+}
+
+struct FwdWorkspace {
+  float* pmax;
+  float* psum;
+  float* ztgt;
+  float* blk_loss;
+  int* blk_cnt;
+  unsigned int* ticket;
+  int64_t Mpad;
+  int n_blk;
+  size_t bytes;
+};
+
+FwdWorkspace carve_fwd(void* base, int64_t M) {
+  FwdWorkspace w;
+  w.Mpad = round_up(M, 256);
+  w.n_blk = static_cast<int>(w.Mpad / 256);
+  uint8_t* p = static_cast<uint8_t*>(base);
+  size_t off = 0;
+  w.pmax = reinterpret_cast<float*>(p + off);
+  off += sizeof(float) * kMaxChunks * w.Mpad;
+  w.psum = reinterpret_cast<float*>(p + off);
+  off += sizeof(float) * kMaxChunks * w.Mpad;
+  w.ztgt = reinterpret_cast<float*>(p + off);
+  off += sizeof(float) * w.Mpad;
+  w.blk_loss = reinterpret_cast<float*>(p + off);
+  off += round_up(sizeof(float) * w.n_blk, 256);
+  w.blk_cnt = reinterpret_cast<int*>(p + off);
+  off += round_up(sizeof(int) * w.n_blk, 256);
+  w.ticket = reinterpret_cast<unsigned int*>(p + off);
+  off += 256;
+  w.bytes = off;
+  return w;
+}
+
+template <int kCG>
+int run_fwd(const void* H, const void* W, const void* bias, const int64_t* targets, int64_t M, int d, int V,
+            float* lse, float* loss_sum, int32_t* n_valid, const FwdWorkspace& ws, int sm_count, cudaStream_t st) {
+  constexpr int BN = 256;
+  constexpr int kStages = (kCG == 1) ? 4 : 6;
+  CUtensorMap tmA, tmB;
+  if (int rc = make_tmap(&tmA, H, d, M, static_cast<uint64_t>(d) * 2, BK, BM)) return rc;
+  if (int rc = make_tmap(&tmB, W, d, V, static_cast<uint64_t>(d) * 2, BK, BN / kCG)) return rc;
+  Sched sc;
+  const int n_mblk = ceil_div(M, BM * kCG);
+  sc.n_ntile = ceil_div(V, BN);
+  int n_chunks;
+  plan_chunks(n_mblk, sc.n_ntile, sm_count / kCG, &n_chunks, &sc.tiles_per_chunk);
+  sc.n_units = n_mblk * n_chunks;
+  sc.n_inner = n_mblk;
+  sc.inner_is_m = 1;
+  sc.n_kblk = ceil_div(d, BK);
+  FwdEpi::Params ep;
+  ep.targets = targets;
+  ep.bias = static_cast<const __nv_bfloat16*>(bias);
+  ep.pmax = ws.pmax;
+  ep.psum = ws.psum;
+  ep.ztgt = ws.ztgt;
+  ep.M = static_cast<int>(M);
+  ep.V = V;
+  ep.Mpad = static_cast<int>(ws.Mpad);
+  FTK_CUDA_CHECK(cudaMemsetAsync(ws.ticket, 0, sizeof(unsigned int), st));
+  if (int rc = launch_umma<kCG, BN, kStages, false, false, FwdEpi>(tmA, tmB, sc, ep, sm_count, st)) return rc;
+  fwd_finalize_kernel<<<ceil_div(M, 256), 256, 0, st>>>(ws.pmax, ws.psum, ws.ztgt, targets, static_cast<int>(M),
+                                                        static_cast<int>(ws.Mpad), n_chunks, lse, ws.blk_loss,
+                                                        ws.blk_cnt, ws.ticket, loss_sum, n_valid);
+  FTK_CUDA_CHECK(cudaGetLastError());
+  return FTK_OK;
+}
+
+constexpr int64_t kDefaultSlabRows = 16384;
+inline int64_t dz_pitch(int V) { return round_up(V, 64); }  // bf16 elements; rows start 128-byte aligned
+
+template <int kCG>
+int run_bwd_slab(const void* H, const void* W, const void* bias, const int64_t* targets, const float* lse,
+                 int64_t rows, int d, int V, float grad_scale, const float* grad_scale_dev, const int32_t* n_valid_dev,
+                 void* dH, void* dW, int dw_dtype, int accumulate, float* dbias, __nv_bfloat16* dz, int sm_count,
+                 cudaStream_t st) {
+  constexpr int BN = 256;
+  constexpr int kStages = (kCG == 1) ? 4 : 6;
+  const int64_t ld = dz_pitch(V);
+  const int n_groups = sm_count / kCG;
+
+  // ---- stage 1: dZ slab = (softmax - onehot) * scale, logits recomputed on the tensor cores
+  {
+    CUtensorMap tmA, tmB;
+    if (int rc = make_tmap(&tmA, H, d, rows, static_cast<uint64_t>(d) * 2, BK, BM)) return rc;
+    if (int rc = make_tmap(&tmB, W, d, V, static_cast<uint64_t>(d) * 2, BK, BN / kCG)) return rc;
+    Sched sc;
+    const int n_mblk = ceil_div(rows, BM * kCG);
+    sc.n_ntile = ceil_div(V, BN);
+    int n_chunks;
+    plan_chunks(n_mblk, sc.n_ntile, n_groups, &n_chunks, &sc.tiles_per_chunk);
+    sc.n_units = n_mblk * n_chunks;
+    sc.n_inner = n_mblk;
+    sc.inner_is_m = 1;
+    sc.n_kblk = ceil_div(d, BK);
+    DzEpi::Params ep;
+    ep.targets = targets;
+    ep.bias = static_cast<const __nv_bfloat16*>(bias);
+    ep.lse = lse;
+    ep.dz = dz;
+    ep.scale_dev = grad_scale_dev;
+    ep.nvalid_dev = n_valid_dev;
+    ep.scale = grad_scale;
+    ep.rows = static_cast<int>(rows);
+    ep.V = V;
+    ep.ld = static_cast<int>(ld);
+    if (int rc = launch_umma<kCG, BN, kStages, false, false, DzEpi>(tmA, tmB, sc, ep, sm_count, st)) return rc;
+  }
+  // ---- stage 2: dH[rows, d] = dZ[rows, V] . W[V, d]
+  {
+    CUtensorMap tmA, tmB;
+    if (int rc = make_tmap(&tmA, dz, V, rows, static_cast<uint64_t>(ld) * 2, BK, BM)) return rc;
+    if (int rc = make_tmap(&tmB, W, d, V, static_cast<uint64_t>(d) * 2, 64, BK)) return rc;
+    Sched sc;
+    const int n_mblk = ceil_div(rows, BM * kCG);
+    sc.n_ntile = ceil_div(d, BN);
+    sc.tiles_per_chunk = 1;
+    sc.n_units = n_mblk * sc.n_ntile;
+    sc.n_inner = sc.n_ntile;  // N tiles of one m block are adjacent: the dZ rows are read from HBM once
+    sc.inner_is_m = 0;
+    sc.n_kblk = ceil_div(V, BK);
+    StoreEpi<false>::Params ep;
+    ep.out = dH;
+    ep.rows = static_cast<int>(rows);
+    ep.cols = d;
+    ep.ld = d;
+    ep.accumulate = 0;
+    if (int rc = launch_umma<kCG, BN, kStages, false, true, StoreEpi<false>>(tmA, tmB, sc, ep, sm_count, st)) return rc;
+  }
+  // ---- stage 3: dW[V, d] (+)= dZ^T[V, rows] . H[rows, d]
+  {
+    CUtensorMap tmA, tmB;
+    if (int rc = make_tmap(&tmA, dz, V, rows, static_cast<uint64_t>(ld) * 2, 64, BK)) return rc;
+    if (int rc = make_tmap(&tmB, H, d, rows, static_cast<uint64_t>(d) * 2, 64, BK)) return rc;
+    Sched sc;
+    const int n_mblk = ceil_div(V, BM * kCG);
+    sc.n_ntile = ceil_div(d, BN);
+    sc.tiles_per_chunk = 1;
+    sc.n_units = n_mblk * sc.n_ntile;
+    sc.n_inner = sc.n_ntile;
+    sc.inner_is_m = 0;
+    sc.n_kblk = ceil_div(rows, BK);
+    if (dw_dtype == FTK_F32) {
+      StoreEpi<true>::Params ep;
+      ep.out = dW;
+      ep.rows = V;
+      ep.cols = d;
+      ep.ld = d;
+      ep.accumulate = accumulate;
+      if (int rc = launch_umma<kCG, BN, kStages, true, true, StoreEpi<true>>(tmA, tmB, sc, ep, sm_count, st)) return rc;
+    } else {
+      StoreEpi<false>::Params ep;
+      ep.out = dW;
+      ep.rows = V;
+      ep.cols = d;
+      ep.ld = d;
+      ep.accumulate = accumulate;
+      if (int rc = launch_umma<kCG, BN, kStages, true, true, StoreEpi<false>>(tmA, tmB, sc, ep, sm_count, st))
+        return rc;
+    }
+  }
+  // ---- optional: dbias += column sums of the slab
+  if (dbias != nullptr) {
+    const int rows_per_block = 256;
+    dim3 grid(ceil_div(V, 256), ceil_div(rows, rows_per_block));
+    dbias_kernel<<<grid, 128, 0, st>>>(dz, static_cast<int>(rows), V, static_cast<int>(ld), rows_per_block, dbias);
+    FTK_CUDA_CHECK(cudaGetLastError());
+  }
+  return FTK_OK;
+}
+
+int check_common(const void* H, const void* W, int64_t M, int d, int V, ftk::DeviceInfo* di) {
+  FTK_REQUIRE(H && W, "lmhead_ce: null H or W");
+  FTK_REQUIRE(M > 0 && M < (int64_t(1) << 30), "lmhead_ce: M=%lld out of range", static_cast<long long>(M));
+  FTK_REQUIRE(d > 0 && d % 64 == 0, "lmhead_ce: d=%d must be a positive multiple of 64", d);
+  FTK_REQUIRE(V > 0 && V <= (1 << 24), "lmhead_ce: V=%d out of range", V);
+  if (int rc = ftk::get_device_info(di)) return rc;
+  if (di->cc_major != 10)
+    return ftk::fail(FTK_EUNSUPPORTED, "lmhead_ce needs an sm_100 device (tcgen05/TMEM); found sm_%d%d", di->cc_major,
+                     di->cc_minor);
+  return FTK_OK;
+}
+
+}  // namespace
+
+extern "C" size_t ftk_lmhead_ce_fwd_workspace(int64_t M, int32_t d, int32_t V) {
+  (void)d;
+  (void)V;
+  if (M <= 0) return 0;
+  return carve_fwd(nullptr, M).bytes;
+}
+
+extern "C" int ftk_lmhead_ce_fwd(const void* H, const void* W, const void* bias, const int64_t* targets, int64_t M,
+                                 int32_t d, int32_t V, float* lse, float* loss_sum, int32_t* n_valid, void* workspace,
+                                 size_t workspace_bytes, void* stream) {
+  ftk::DeviceInfo di;
+  if (int rc = check_common(H, W, M, d, V, &di)) return rc;
+  FTK_REQUIRE(targets && lse && loss_sum && n_valid && workspace, "ftk_lmhead_ce_fwd: null pointer argument");
+  FTK_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "ftk_lmhead_ce_fwd: workspace must be 256-byte aligned");
+  const FwdWorkspace ws = carve_fwd(workspace, M);
+  if (workspace_bytes < ws.bytes)
+    return ftk::fail(FTK_EWORKSPACE, "ftk_lmhead_ce_fwd: workspace %zu bytes < required %zu", workspace_bytes,
+                     ws.bytes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (cta_group() == 2 && di.sm_count >= 2)
+    return run_fwd<2>(H, W, bias, targets, M, d, V, lse, loss_sum, n_valid, ws, di.sm_count, st);
+  return run_fwd<1>(H, W, bias, targets, M, d, V, lse, loss_sum, n_valid, ws, di.sm_count, st);
+}
+
+extern "C" size_t ftk_lmhead_ce_bwd_workspace(int64_t M, int32_t d, int32_t V, int64_t slab_rows) {
+  (void)d;
+  if (M <= 0 || V <= 0) return 0;
+  int64_t rows = slab_rows > 0 ? slab_rows : kDefaultSlabRows;
+  if (rows > M) rows = M;
+  rows = round_up(rows, 256);
+  return static_cast<size_t>(rows) * static_cast<size_t>(dz_pitch(V)) * 2;
+}
+
+extern "C" int ftk_lmhead_ce_bwd(const void* H, const void* W, const void* bias, const int64_t* targets,
+                                 const float* lse, int64_t M, int32_t d, int32_t V, float grad_scale,
+                                 const float* grad_scale_dev, const int32_t* n_valid_dev, void* dH, void* dW,
+                                 int32_t dw_dtype, int32_t accumulate, float* dbias, void* workspace,
+                                 size_t workspace_bytes, void* stream) {
+  ftk::DeviceInfo di;
+  if (int rc = check_common(H, W, M, d, V, &di)) return rc;
+  FTK_REQUIRE(targets && lse && dH && dW && workspace, "ftk_lmhead_ce_bwd: null pointer argument");
+  FTK_REQUIRE(dw_dtype == FTK_BF16 || dw_dtype == FTK_F32, "ftk_lmhead_ce_bwd: bad dw_dtype %d", dw_dtype);
+  FTK_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "ftk_lmhead_ce_bwd: workspace must be 256-byte aligned");
+  FTK_REQUIRE((reinterpret_cast<uintptr_t>(dH) & 15) == 0 && (reinterpret_cast<uintptr_t>(dW) & 15) == 0,
+              "ftk_lmhead_ce_bwd: dH/dW must be 16-byte aligned");
+  const int64_t ld = dz_pitch(V);
+  int64_t slab = static_cast<int64_t>(workspace_bytes / (static_cast<size_t>(ld) * 2));
+  if (slab >= M)
+    slab = M;
+  else
+    slab = slab / 256 * 256;
+  if (slab <= 0)
+    return ftk::fail(FTK_EWORKSPACE, "ftk_lmhead_ce_bwd: workspace %zu bytes holds no 256-row dZ slab (pitch %lld)",
+                     workspace_bytes, static_cast<long long>(ld));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dbias != nullptr && !accumulate) FTK_CUDA_CHECK(cudaMemsetAsync(dbias, 0, sizeof(float) * V, st));
+  const bool pair = (cta_group() == 2 && di.sm_count >= 2);
+  const size_t dh_esize = 2;
+  for (int64_t r0 = 0; r0 < M; r0 += slab) {
+    const int64_t rows = (M - r0 < slab) ? (M - r0) : slab;
+    const void* Hs = static_cast<const uint8_t*>(H) + static_cast<size_t>(r0) * d * 2;
+    void* dHs = static_cast<uint8_t*>(dH) + static_cast<size_t>(r0) * d * dh_esize;
+    const int acc = (accumulate || r0 > 0) ? 1 : 0;
+    int rc;
+    if (pair)
+      rc = run_bwd_slab<2>(Hs, W, bias, targets + r0, lse + r0, rows, d, V, grad_scale, grad_scale_dev, n_valid_dev,
+                           dHs, dW, dw_dtype, acc, dbias, static_cast<__nv_bfloat16*>(workspace), di.sm_count, st);
+    else
+      rc = run_bwd_slab<1>(Hs, W, bias, targets + r0, lse + r0, rows, d, V, grad_scale, grad_scale_dev, n_valid_dev,
+                           dHs, dW, dw_dtype, acc, dbias, static_cast<__nv_bfloat16*>(workspace), di.sm_count, st);
+    if (rc) return rc;
+  }
+  return FTK_OK;
+}

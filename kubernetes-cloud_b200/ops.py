@@ -1,0 +1,184 @@
+"""PyTorch custom ops over the C ABI (include/ftk.h).  PyTorch is plumbing here: it owns device memory and the
+current stream; all arithmetic happens inside lib/libftk.so.  No op has a CPU or eager fallback.
+
+  torch.ops.ftk.gather_windows   -> ftk_gather_windows   (replaces FT.py:662-692, :1030-1035, :476-477)
+  torch.ops.ftk.lmhead_ce_fwd    -> ftk_lmhead_ce_fwd    (replaces HF lm_head + ForCausalLMLoss, FT.py:479)
+  torch.ops.ftk.lmhead_ce_bwd    -> ftk_lmhead_ce_bwd    (their autograd)
+  fused_lmhead_ce(hidden, weight, bias, targets) -> mean loss, differentiable w.r.t. hidden / weight / bias
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+
+IGNORE = -100
+_launches = 0  # kernels launched through this module (bench.py reports it as gpu_launches)
+
+
+def launch_count() -> int:
+    return _launches
+
+
+def _stream(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _need_cuda(*ts: Optional[torch.Tensor]) -> None:
+    for t in ts:
+        if t is not None and not t.is_cuda:
+            raise _lib.FtkError("ftk ops run on CUDA tensors only (there is no CPU fallback)")
+
+
+def _ptr(t: Optional[torch.Tensor]) -> int:
+    return 0 if t is None else t.data_ptr()
+
+
+@torch.library.custom_op("ftk::gather_windows", mutates_args=())
+def gather_windows(tokens: torch.Tensor, ctx_idx: torch.Tensor, T: int, pad_id: int, pad_is_eos: bool,
+                   shift_labels: bool) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
+    """tokens: flat uint16 (or int16 view) token stream on the GPU; ctx_idx: int64 [B] on the GPU.
+    Returns input_ids int64 [B,T], labels int64 [B,T] (-100 where masked; shifted if asked), attention_mask
+    bool [B,T], n_valid int32 [B]."""
+    global _launches
+    _need_cuda(tokens, ctx_idx)
+    if tokens.element_size() != 2 or not tokens.is_contiguous():
+        raise _lib.FtkError("tokens must be a contiguous 16-bit tensor")
+    if ctx_idx.dtype != torch.int64 or not ctx_idx.is_contiguous():
+        raise _lib.FtkError("ctx_idx must be a contiguous int64 tensor")
+    n_ctx = tokens.numel() // T
+    B = ctx_idx.numel()
+    dev = tokens.device
+    ids = torch.empty((B, T), dtype=torch.int64, device=dev)
+    labels = torch.empty((B, T), dtype=torch.int64, device=dev)
+    mask = torch.empty((B, T), dtype=torch.bool, device=dev)
+    n_valid = torch.empty((B,), dtype=torch.int32, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().ftk_gather_windows(tokens.data_ptr(), n_ctx, T, ctx_idx.data_ptr(), B, pad_id,
+                                           int(pad_is_eos), int(shift_labels), ids.data_ptr(), labels.data_ptr(),
+                                           mask.data_ptr(), n_valid.data_ptr(), _stream(tokens))
+    _lib.check(rc, "ftk_gather_windows")
+    _launches += 1
+    return ids, labels, mask, n_valid
+
+
+@gather_windows.register_fake
+def _(tokens, ctx_idx, T, pad_id, pad_is_eos, shift_labels):
+    B = ctx_idx.numel()
+    return (tokens.new_empty((B, T), dtype=torch.int64), tokens.new_empty((B, T), dtype=torch.int64),
+            tokens.new_empty((B, T), dtype=torch.bool), tokens.new_empty((B,), dtype=torch.int32))
+
+
+def _check_hw(H: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor], targets: torch.Tensor) -> None:
+    _need_cuda(H, W, bias, targets)
+    if H.dtype != torch.bfloat16 or W.dtype != torch.bfloat16:
+        raise _lib.FtkError("hidden and weight must be bfloat16")
+    if bias is not None and bias.dtype != torch.bfloat16:
+        raise _lib.FtkError("bias must be bfloat16")
+    if H.dim() != 2 or W.dim() != 2 or H.shape[1] != W.shape[1]:
+        raise _lib.FtkError(f"bad shapes hidden {tuple(H.shape)} weight {tuple(W.shape)}")
+    if not (H.is_contiguous() and W.is_contiguous() and targets.is_contiguous()):
+        raise _lib.FtkError("hidden, weight and targets must be contiguous")
+    if targets.dtype != torch.int64 or targets.numel() != H.shape[0]:
+        raise _lib.FtkError("targets must be int64 with one entry per hidden row")
+
+
+@torch.library.custom_op("ftk::lmhead_ce_fwd", mutates_args=())
+def lmhead_ce_fwd(H: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor],
+                  targets: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """Returns (loss_sum fp32 [1], n_valid int32 [1], lse fp32 [M]) for logits = H @ W.T (+ bias) without ever
+    writing the logits to HBM."""
+    global _launches
+    _check_hw(H, W, bias, targets)
+    M, d = H.shape
+    V = W.shape[0]
+    dev = H.device
+    lse = torch.empty((M,), dtype=torch.float32, device=dev)
+    loss_sum = torch.empty((1,), dtype=torch.float32, device=dev)
+    n_valid = torch.empty((1,), dtype=torch.int32, device=dev)
+    L = _lib.lib()
+    ws_bytes = L.ftk_lmhead_ce_fwd_workspace(M, d, V)
+    ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        rc = L.ftk_lmhead_ce_fwd(H.data_ptr(), W.data_ptr(), _ptr(bias), targets.data_ptr(), M, d, V, lse.data_ptr(),
+                                 loss_sum.data_ptr(), n_valid.data_ptr(), ws.data_ptr(), ws_bytes, _stream(H))
+    _lib.check(rc, "ftk_lmhead_ce_fwd")
+    _launches += 2  # fused GEMM+softmax kernel, finalize kernel
+    return loss_sum, n_valid, lse
+
+
+@lmhead_ce_fwd.register_fake
+def _(H, W, bias, targets):
+    return (H.new_empty((1,), dtype=torch.float32), H.new_empty((1,), dtype=torch.int32),
+            H.new_empty((H.shape[0],), dtype=torch.float32))
+
+
+_slab_rows = 0  # 0 = library default; tests shrink it to exercise the multi-slab path
+
+
+def set_bwd_slab_rows(rows: int) -> None:
+    global _slab_rows
+    _slab_rows = int(rows)
+
+
+@torch.library.custom_op("ftk::lmhead_ce_bwd", mutates_args=())
+def lmhead_ce_bwd(H: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor], targets: torch.Tensor,
+                  lse: torch.Tensor, grad_out: Optional[torch.Tensor], n_valid: Optional[torch.Tensor],
+                  grad_scale: float, dw_fp32: bool) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """Returns (dH bf16 [M,d], dW [V,d] bf16 or fp32, dbias fp32 [V] or empty).
+    dZ = (softmax - onehot) * grad_scale * grad_out / n_valid on valid rows."""
+    global _launches
+    _check_hw(H, W, bias, targets)
+    _need_cuda(lse, grad_out, n_valid)
+    M, d = H.shape
+    V = W.shape[0]
+    dev = H.device
+    dH = torch.empty((M, d), dtype=torch.bfloat16, device=dev)
+    dW = torch.empty((V, d), dtype=torch.float32 if dw_fp32 else torch.bfloat16, device=dev)
+    dbias = torch.empty((V if bias is not None else 0,), dtype=torch.float32, device=dev)
+    if grad_out is not None:
+        grad_out = grad_out.to(torch.float32).contiguous()
+    L = _lib.lib()
+    ws_bytes = L.ftk_lmhead_ce_bwd_workspace(M, d, V, _slab_rows)
+    ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        rc = L.ftk_lmhead_ce_bwd(H.data_ptr(), W.data_ptr(), _ptr(bias), targets.data_ptr(), lse.data_ptr(), M, d, V,
+                                 grad_scale, _ptr(grad_out), _ptr(n_valid), dH.data_ptr(), dW.data_ptr(),
+                                 _lib.FTK_F32 if dw_fp32 else _lib.FTK_BF16, 0,
+                                 dbias.data_ptr() if bias is not None else 0, ws.data_ptr(), ws_bytes, _stream(H))
+    _lib.check(rc, "ftk_lmhead_ce_bwd")
+    slab = _slab_rows if _slab_rows > 0 else 16384
+    n_slabs = (M + slab - 1) // slab
+    _launches += n_slabs * (3 + (1 if bias is not None else 0))
+    return dH, dW, dbias
+
+
+@lmhead_ce_bwd.register_fake
+def _(H, W, bias, targets, lse, grad_out, n_valid, grad_scale, dw_fp32):
+    return (torch.empty_like(H), W.new_empty(W.shape, dtype=torch.float32 if dw_fp32 else torch.bfloat16),
+            H.new_empty((W.shape[0] if bias is not None else 0,), dtype=torch.float32))
+
+
+class _FusedLmHeadCE(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, hidden, weight, bias, targets):
+        loss_sum, n_valid, lse = torch.ops.ftk.lmhead_ce_fwd(hidden, weight, bias, targets)
+        ctx.save_for_backward(hidden, weight, bias, targets, lse, n_valid)
+        # mean over valid rows (transformers fixed_cross_entropy, reduction="mean"); 0/0 -> NaN as in the reference
+        return (loss_sum / n_valid.to(torch.float32)).reshape(())
+
+    @staticmethod
+    def backward(ctx, grad_out):
+        hidden, weight, bias, targets, lse, n_valid = ctx.saved_tensors
+        dH, dW, dbias = torch.ops.ftk.lmhead_ce_bwd(hidden, weight, bias, targets, lse, grad_out.reshape(1), n_valid,
+                                                    1.0, False)
+        return dH, dW, (dbias.to(bias.dtype) if bias is not None else None), None
+
+
+def fused_lmhead_ce(hidden: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor],
+                    targets: torch.Tensor) -> torch.Tensor:
+    """Mean causal-LM cross-entropy of logits = hidden @ weight.T (+ bias) against already shifted targets
+    (-100 = ignore).  hidden [M,d] bf16, weight [V,d] bf16.  Differentiable; the logits never reach HBM."""
+    return _FusedLmHeadCE.apply(hidden, weight, bias, targets)
