@@ -55,6 +55,8 @@ def gather_windows(tokens: torch.Tensor, ctx_idx: torch.Tensor, T: int, pad_id: 
     labels = torch.empty((B, T), dtype=torch.int64, device=dev)
     mask = torch.empty((B, T), dtype=torch.bool, device=dev)
     n_valid = torch.empty((B,), dtype=torch.int32, device=dev)
+    if B == 0:
+        return ids, labels, mask, n_valid
     with torch.cuda.device(dev):
         rc = _lib.lib().ftk_gather_windows(tokens.data_ptr(), n_ctx, T, ctx_idx.data_ptr(), B, pad_id,
                                            int(pad_is_eos), int(shift_labels), ids.data_ptr(), labels.data_ptr(),

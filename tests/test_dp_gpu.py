@@ -1,0 +1,51 @@
+"""G4 gradient sync through the C ABI's NCCL path on the GPUs that are present (1 on the test box)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def test_grad_sync_ftk_world1_prescale_and_overlap_stream(cuda_dev):
+    from kubernetes_cloud_b200.dp import GradSync
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(64, 128), torch.nn.GELU(), torch.nn.Linear(128, 64)).cuda().to(torch.bfloat16)
+    ref = [p.detach().clone().float().requires_grad_(True) for p in model.parameters()]
+    sync = GradSync(model.parameters(), 0, 1, bucket_bytes=16 << 10, backend="ftk", average=True)
+    x = torch.randn(32, 64, device="cuda", dtype=torch.bfloat16)
+    sync.zero_grad()
+    with sync.no_sync():
+        model(x).float().pow(2).mean().backward()
+    assert sync.launched == 0
+    model(x).float().pow(2).mean().backward()
+    sync.finish()
+    torch.cuda.synchronize()
+    assert sync.launched == len(sync.buckets) >= 2
+    # world 1: the reduced gradient is the locally accumulated one (two identical micro-batches)
+    model2 = torch.nn.Sequential(torch.nn.Linear(64, 128), torch.nn.GELU(), torch.nn.Linear(128, 64)).cuda().to(torch.bfloat16)
+    with torch.no_grad():
+        for p, q in zip(model2.parameters(), ref):
+            p.copy_(q)
+    for _ in range(2):
+        model2(x).float().pow(2).mean().backward()
+    for p, q in zip(model.parameters(), model2.parameters()):
+        assert torch.allclose(p.grad.float(), q.grad.float(), rtol=2e-2, atol=1e-4)
+    sync.close()
+
+
+def test_dp_allreduce_c_abi_scales_in_place(cuda_dev):
+    import ctypes
+    from kubernetes_cloud_b200 import _lib
+    L = _lib.lib()
+    buf = ctypes.create_string_buffer(128)
+    _lib.check(L.ftk_dp_unique_id(buf), "ftk_dp_unique_id")
+    h = ctypes.c_void_p()
+    _lib.check(L.ftk_dp_init(buf, 0, 1, ctypes.byref(h)), "ftk_dp_init")
+    s = torch.cuda.current_stream().cuda_stream
+    for dt, code, n in ((torch.float32, _lib.FTK_F32, 1003), (torch.bfloat16, _lib.FTK_BF16, 4099)):
+        x = torch.arange(n, device="cuda", dtype=torch.float32).to(dt)
+        want = (x.float() * 0.25).to(dt)
+        _lib.check(L.ftk_dp_allreduce(h, x.data_ptr(), n, code, 0.25, s), "ftk_dp_allreduce")
+        _lib.check(L.ftk_dp_join(h, s), "ftk_dp_join")
+        torch.cuda.synchronize()
+        assert torch.equal(x, want)
+    _lib.check(L.ftk_dp_destroy(h), "ftk_dp_destroy")
