@@ -99,6 +99,35 @@ int ftk_lmhead_ce_fwd(const void* H, const void* W, const void* bias, const int6
                       size_t workspace_bytes, void* stream);
 
 /*
+ * The same forward for callers that cannot allocate device memory. It has no
+ * counterpart in the reference.
+ *
+ * ftk_lmhead_ce_fwd wants a workspace, and getting one means cudaMalloc or a
+ * framework allocator somewhere in the caller. Two kinds of host cannot do
+ * that: a plugin living inside a runtime that reserved all of HBM for its own
+ * pool at start-up and gives plugins no allocator, and a latency-critical loop
+ * that must avoid the device-wide synchronisation cudaMalloc/cudaFree imply.
+ * This variant keeps its scratch in a fixed array inside the library's device
+ * image (about 4.3 MB per GPU that loads the library, held until exit), so the
+ * call itself performs no allocation of any kind; inputs and outputs are still
+ * the caller's buffers.
+ *
+ *   - M must be <= FTK_STATIC_MAX_ROWS; larger M fails with FTK_EWORKSPACE and
+ *     a message naming the limit (use ftk_lmhead_ce_fwd for those).
+ *   - The first call on each device looks up the array's device address
+ *     (cudaGetSymbolAddress, with that device current) and caches it. Make that
+ *     first call before starting any stream capture.
+ *   - All calls share the one array and it keeps the previous call's contents.
+ *     What has to start at zero is cleared on `stream` at the start of every
+ *     call. Calls whose kernels can overlap on the GPU (two streams, two
+ *     threads) would race on it: serialise them.
+ * Results are identical to ftk_lmhead_ce_fwd.
+ */
+#define FTK_STATIC_MAX_ROWS 16384
+int ftk_lmhead_ce_fwd_static(const void* H, const void* W, const void* bias, const int64_t* targets, int64_t M,
+                             int32_t d, int32_t V, float* lse, float* loss_sum, int32_t* n_valid, void* stream);
+
+/*
  * Fused backward of the above (autograd of lm_head + cross_entropy in the
  * reference, reached from loss.backward() inside HF Trainer.training_step).
  *   dZ = (softmax(z) - onehot(target)) * scale for valid rows, 0 for ignored,

@@ -25,6 +25,8 @@ SIGNATURES = {
     "ftk_lmhead_ce_fwd_workspace": (c_size_t, [c_int64, c_int32, c_int32]),
     "ftk_lmhead_ce_fwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p,
                                     c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "ftk_lmhead_ce_fwd_static": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p,
+                                           c_void_p, c_void_p, c_void_p]),
     "ftk_lmhead_ce_bwd_workspace": (c_size_t, [c_int64, c_int32, c_int32, c_int64]),
     "ftk_lmhead_ce_bwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32,
                                     c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_void_p,

@@ -929,3 +929,69 @@ extern "C" int ftk_lmhead_ce_bwd(const void* H, const void* W, const void* bias,
   }
   return FTK_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Forward pass for callers that cannot allocate device memory.
+//
+// ftk_lmhead_ce_fwd needs a caller-provided workspace, which in practice means a cudaMalloc (or a framework
+// allocator call) somewhere up the stack.  Some hosts have no way to make one: a plugin embedded in a serving or
+// training runtime that claimed all of HBM for its own pool at start-up and hands its plugins no allocator, or a
+// latency-critical loop that must not hit the device-wide synchronisation cudaMalloc/cudaFree imply.  For them the
+// scratch below is part of the library image: a fixed array in device global memory, created when the module is
+// loaded on a GPU and held until the process exits (every GPU that loads the library pays for it once).
+//
+// Limit: M <= FTK_STATIC_MAX_ROWS (16,384 rows, one 8 x 2048 micro-batch); larger calls are rejected.
+// The array is shared by every call and keeps whatever the last call left in it.  The only part that must start
+// at zero -- the finalize kernel's arrival counter -- is cleared on the stream at the start of each call; the
+// per-chunk statistics are fully rewritten before they are read.  Two calls whose kernels overlap on the GPU
+// (different streams, or different host threads) would write the same scratch and race: serialise them.
+namespace {
+
+constexpr int64_t kStaticMaxRows = FTK_STATIC_MAX_ROWS;
+// same carve-up as carve_fwd(): 2 * kMaxChunks + 1 floats per (padded) row, block partials, counter
+constexpr size_t kStaticScratchBytes =
+    sizeof(float) * (2 * kMaxChunks + 1) * static_cast<size_t>(kStaticMaxRows) + 2 * 256 + 256;
+
+static __device__ __align__(256) unsigned char g_fwd_static_scratch[kStaticScratchBytes];
+
+// In host code `g_fwd_static_scratch` is only a handle for the runtime, not a device address; the address a kernel
+// can use comes from cudaGetSymbolAddress, looked up once per device with that device current.
+int static_scratch_ptr(void** out) {
+  static void* ptr_of_device[64] = {nullptr};
+  int dev = 0;
+  FTK_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return ftk::fail(FTK_EINVAL, "device ordinal %d out of range", dev);
+  if (ptr_of_device[dev] == nullptr) {
+    void* p = nullptr;
+    FTK_CUDA_CHECK(cudaGetSymbolAddress(&p, g_fwd_static_scratch));
+    if (p == nullptr) return ftk::fail(FTK_ECUDA, "cudaGetSymbolAddress returned a null scratch address");
+    ptr_of_device[dev] = p;
+  }
+  *out = ptr_of_device[dev];
+  return FTK_OK;
+}
+
+}  // namespace
+
+extern "C" int ftk_lmhead_ce_fwd_static(const void* H, const void* W, const void* bias, const int64_t* targets,
+                                        int64_t M, int32_t d, int32_t V, float* lse, float* loss_sum,
+                                        int32_t* n_valid, void* stream) {
+  ftk::DeviceInfo di;
+  if (int rc = check_common(H, W, M, d, V, &di)) return rc;
+  FTK_REQUIRE(targets && lse && loss_sum && n_valid, "ftk_lmhead_ce_fwd_static: null pointer argument");
+  if (M > kStaticMaxRows)
+    return ftk::fail(FTK_EWORKSPACE,
+                     "ftk_lmhead_ce_fwd_static: M=%lld exceeds the built-in scratch limit of %lld rows; use "
+                     "ftk_lmhead_ce_fwd with a caller-provided workspace",
+                     static_cast<long long>(M), static_cast<long long>(kStaticMaxRows));
+  void* scratch = nullptr;
+  if (int rc = static_scratch_ptr(&scratch)) return rc;
+  const FwdWorkspace ws = carve_fwd(scratch, M);
+  if (ws.bytes > kStaticScratchBytes)
+    return ftk::fail(FTK_EWORKSPACE, "ftk_lmhead_ce_fwd_static: internal scratch too small (%zu > %zu)", ws.bytes,
+                     kStaticScratchBytes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (cta_group() == 2 && di.sm_count >= 2)
+    return run_fwd<2>(H, W, bias, targets, M, d, V, lse, loss_sum, n_valid, ws, di.sm_count, st);
+  return run_fwd<1>(H, W, bias, targets, M, d, V, lse, loss_sum, n_valid, ws, di.sm_count, st);
+}
