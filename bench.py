@@ -346,19 +346,41 @@ def main_gpu(args) -> None:
     # ================= bulk gather bandwidth (HBM roofline of G1; outside the step: one step's gather is 0.3 MB) ====
     n_bulk = 4096 * 8  # 2^26 tokens per launch
     big_idx = torch.randint(0, N_CTX_FILE, (n_bulk,), device=dev)
+
+    def bulk_gather_gbs() -> float:
+        for _ in range(2):
+            out = torch.ops.ftk.gather_windows(tokens, big_idx, CTX, PAD_ID, True, True)
+        del out
+        torch.cuda.synchronize(dev)
+        g0 = torch.cuda.Event(enable_timing=True)
+        g1 = torch.cuda.Event(enable_timing=True)
+        g0.record(stream)
+        for _ in range(3):
+            out = torch.ops.ftk.gather_windows(tokens, big_idx, CTX, PAD_ID, True, True)
+        g1.record(stream)
+        torch.cuda.synchronize(dev)
+        del out
+        return 19.0 * n_bulk * CTX / (g0.elapsed_time(g1) / 3 / 1e3) / 1e9
+
+    gather_gbs = bulk_gather_gbs()
+    # calibration: a pure write stream of the same size (cudaMemset-style fill), the ceiling for a kernel that
+    # writes 17 of every 19 bytes; the copy figure in MEASURED_PEAKS.json is half reads
+    fill = torch.empty(int(19 * n_bulk * CTX) // 8, dtype=torch.int64, device=dev)
     for _ in range(2):
-        out = torch.ops.ftk.gather_windows(tokens, big_idx, CTX, PAD_ID, True, True)
-    del out
+        fill.zero_()
     torch.cuda.synchronize(dev)
-    g0 = torch.cuda.Event(enable_timing=True)
-    g1 = torch.cuda.Event(enable_timing=True)
-    g0.record(stream)
+    z0 = torch.cuda.Event(enable_timing=True)
+    z1 = torch.cuda.Event(enable_timing=True)
+    z0.record(stream)
     for _ in range(3):
-        out = torch.ops.ftk.gather_windows(tokens, big_idx, CTX, PAD_ID, True, True)
-    g1.record(stream)
+        fill.zero_()
+    z1.record(stream)
     torch.cuda.synchronize(dev)
-    gather_gbs = 19.0 * n_bulk * CTX / (g0.elapsed_time(g1) / 3 / 1e3) / 1e9
-    del out
+    write_ceiling_gbs = fill.numel() * 8 / (z0.elapsed_time(z1) / 3 / 1e3) / 1e9
+    del fill
+    os.environ["FTK_GATHER_VARIANT"] = "direct"
+    gather_direct_gbs = bulk_gather_gbs()
+    del os.environ["FTK_GATHER_VARIANT"]
 
     if handle is not None:
         L.ftk_dp_destroy(handle)
@@ -399,7 +421,9 @@ def main_gpu(args) -> None:
                            "frac_of_nominal_2250": 3 * flops_fwd / ((fwd_ms + bwd_ms) / 1e3) / 1e12 / 2250.0,
                            "note": "algorithmic 6MVd over forward + backward time"},
         "roofline_gather": {"bound": "hbm", "achieved": gather_gbs, "peak": peaks["hbm"], "unit": "GB/s",
-                            "frac": gather_gbs / peaks["hbm"], "note": "bulk launch of 2^26 tokens, 19 B/token"},
+                            "frac": gather_gbs / peaks["hbm"], "note": "bulk launch of 2^26 tokens, 19 B/token",
+                            "direct_variant_gbs": gather_direct_gbs, "write_only_fill_gbs": write_ceiling_gbs,
+                            "frac_of_write_only_fill": gather_gbs / write_ceiling_gbs},
         "e2e": {"value": e2e_value, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms / args.steps,
                 "note": "token windows + hidden states from pinned host memory each step, loss and count read back"},

@@ -33,21 +33,28 @@ constexpr float kLn2 = 0.6931471805599453f;
 constexpr int kMaxChunks = 32;  // upper bound on vocabulary chunks (sizes the forward workspace)
 
 // Work decomposition. A unit is (m block, chunk of consecutive N tiles); units are dealt round-robin to CTAs
-// (or CTA pairs). Consecutive unit ids share the outer index, so CTAs running at the same time share operand
-// tiles in L2.
+// (or CTA pairs), so the units running at any moment are ~one wave of consecutive unit ids. The ids are ordered so
+// that such a wave covers a group of `m_group` m blocks times a few consecutive chunks: the group's A blocks
+// (m_group x rows x K) stay L2-resident while every chunk sweeps over them, and each B chunk is shared by the
+// m_group clusters that sweep it together. m_group = 1 gives "all N tiles of one m block first".
 struct Sched {
   int n_units;
-  int n_inner;          // units per outer index
-  int inner_is_m;       // 1: unit -> (chunk = outer, m_blk = inner); 0: (m_blk = outer, chunk = inner)
+  int n_mblk;           // m blocks (of BM * kCG rows)
+  int n_chunks;         // chunks per m block
+  int m_group;          // m blocks per group
   int tiles_per_chunk;  // N tiles per unit
   int n_ntile;          // N tiles in total
   int n_kblk;           // K blocks of BK
 };
 
 __device__ __forceinline__ void decode_unit(const Sched& sc, int u, int& m_blk, int& chunk) {
-  const int outer = u / sc.n_inner, inner = u - outer * sc.n_inner;
-  m_blk = sc.inner_is_m ? inner : outer;
-  chunk = sc.inner_is_m ? outer : inner;
+  const int per_group = sc.m_group * sc.n_chunks;
+  const int grp = u / per_group;
+  const int r = u - grp * per_group;
+  const int m_first = grp * sc.m_group;
+  const int gm = min(sc.m_group, sc.n_mblk - m_first);  // the last group may be smaller
+  chunk = r / gm;
+  m_blk = m_first + (r - chunk * gm);
 }
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
@@ -59,8 +66,16 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 // Each epilogue thread owns one accumulator row. tile() reads the BN fp32 columns of that row from TMEM in
 // groups of 32 and must finish all TMEM loads before returning (the caller then frees the accumulator stage).
 
+// Per-thread context the kernel hands to an epilogue: this warp's TMEM lane quarter, lane id and a pointer to the
+// epilogue's own shared-memory staging area (Epi::kSmemBytes bytes, 1024-byte aligned).
+struct EpiCtx {
+  uint8_t* smem;
+  int q, lane;
+};
+
 // Forward: online softmax statistics over this unit's vocabulary chunk.
 struct FwdEpi {
+  static constexpr uint32_t kSmemBytes = 0;
   struct Params {
     const int64_t* targets;     // [M]
     const __nv_bfloat16* bias;  // [V] or null
@@ -85,7 +100,7 @@ struct FwdEpi {
     st.tgt = (row < p.M) ? static_cast<int>(p.targets[row]) : -1;
   }
   template <int BN>
-  static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0) {
+  static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0, const EpiCtx&) {
 #pragma unroll 1
     for (int c = 0; c < BN / 32; ++c) {
       const int col0 = n0 + c * 32;
@@ -130,15 +145,18 @@ struct FwdEpi {
       if (st.has) p.ztgt[st.row] = st.zt;
     }
   }
+  static __device__ __forceinline__ void finish(const EpiCtx&) {}
 };
 
 // Backward stage 1: dZ tile from the recomputed logits.
 struct DzEpi {
+  // Staging for the TMA stores: per epilogue warp two [32 rows x 128 B] buffers in the 128-byte swizzle layout.
+  static constexpr uint32_t kSmemBytes = 4 * 2 * 4096;
   struct Params {
+    CUtensorMap tm_out;         // dZ slab as bf16 [rows][ld], box 64 columns x 32 rows, 128-byte swizzle
     const int64_t* targets;     // [rows] (slab-relative)
     const __nv_bfloat16* bias;  // [V] or null
     const float* lse;           // [rows]
-    __nv_bfloat16* dz;          // [rows][ld]
     const float* scale_dev;     // optional device scalar multiplied into scale
     const int32_t* nvalid_dev;  // optional device count divided out of scale
     float scale;
@@ -147,6 +165,7 @@ struct DzEpi {
   struct State {
     float l2, sc;
     int tgt, row;
+    uint32_t nstore;
   };
   template <int BN>
   static __device__ __forceinline__ void begin_unit(State& st, const Params& p, int row, int) {
@@ -164,45 +183,68 @@ struct DzEpi {
     }
   }
   template <int BN>
-  static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0) {
+  static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0, const EpiCtx& cx) {
+    uint8_t* warp_buf = cx.smem + cx.q * 8192;
+    const int row0 = st.row - cx.lane;  // first row of this warp's 32-row band
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
-      const int col0 = n0 + c * 32;
+    for (int g = 0; g < BN / 64; ++g) {
+      const int col0 = n0 + g * 64;
       if (col0 >= p.ld) break;  // warp-uniform
-      float v[32];
-      tmem_ld32(taddr + c * 32, v);
-      tmem_ld_wait();
-      if (p.bias != nullptr) {
+      uint8_t* buf = warp_buf + (st.nstore & 1) * 4096;
+      // the store issued two groups ago out of this buffer must have finished reading it
+      if (cx.lane == 0) tma_store_wait_read<1>();
+      __syncwarp();
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
-          if (col0 + j < p.V) v[j] += __bfloat162float(__ldg(p.bias + col0 + j));
-      }
-      uint32_t w[16];
+      for (int h = 0; h < 2; ++h) {
+        const int c0 = col0 + h * 32;
+        float v[32];
+        tmem_ld32(taddr + g * 64 + h * 32, v);
+        tmem_ld_wait();
+        if (p.bias != nullptr) {
 #pragma unroll
-      for (int j = 0; j < 32; j += 2) {
-        float g0 = exp2f(fmaf(v[j], kLog2e, st.l2));
-        float g1 = exp2f(fmaf(v[j + 1], kLog2e, st.l2));
-        g0 = (col0 + j == st.tgt) ? g0 - 1.f : g0;
-        g1 = (col0 + j + 1 == st.tgt) ? g1 - 1.f : g1;
-        g0 = (col0 + j < p.V) ? g0 * st.sc : 0.f;
-        g1 = (col0 + j + 1 < p.V) ? g1 * st.sc : 0.f;
-        w[j >> 1] = pack_bf16x2(g0, g1);
-      }
-      if (st.row < p.rows) {
-        uint4* dst = reinterpret_cast<uint4*>(p.dz + static_cast<size_t>(st.row) * p.ld + col0);
+          for (int j = 0; j < 32; ++j)
+            if (c0 + j < p.V) v[j] += __bfloat162float(__ldg(p.bias + c0 + j));
+        }
+        uint32_t w[16];
 #pragma unroll
-        for (int q = 0; q < 4; ++q)
-          if (col0 + q * 8 < p.ld) dst[q] = make_uint4(w[4 * q], w[4 * q + 1], w[4 * q + 2], w[4 * q + 3]);
+        for (int j = 0; j < 32; j += 2) {
+          float g0 = exp2f(fmaf(v[j], kLog2e, st.l2));
+          float g1 = exp2f(fmaf(v[j + 1], kLog2e, st.l2));
+          g0 = (c0 + j == st.tgt) ? g0 - 1.f : g0;
+          g1 = (c0 + j + 1 == st.tgt) ? g1 - 1.f : g1;
+          g0 = (c0 + j < p.V) ? g0 * st.sc : 0.f;  // pad columns [V, ld) are written as zeros
+          g1 = (c0 + j + 1 < p.V) ? g1 * st.sc : 0.f;
+          w[j >> 1] = pack_bf16x2(g0, g1);
+        }
+        // row `lane` of the box, 16-byte chunk c at position c ^ (lane & 7): the layout TMA expects for
+        // SWIZZLE_128B, and conflict-free for the 8 lanes of each store phase
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq) {
+          const int c = h * 4 + qq;
+          uint4* dst = reinterpret_cast<uint4*>(buf + cx.lane * 128 + ((c ^ (cx.lane & 7)) << 4));
+          *dst = make_uint4(w[4 * qq], w[4 * qq + 1], w[4 * qq + 2], w[4 * qq + 3]);
+        }
       }
+      fence_async_shared();  // make the generic-proxy smem writes visible to the TMA engine
+      __syncwarp();
+      if (cx.lane == 0) {
+        tma_store_2d(&p.tm_out, buf, col0, row0);  // rows >= p.rows / columns >= ld are clipped by the tensor map
+        tma_store_commit();
+      }
+      ++st.nstore;
     }
   }
   template <int BN>
   static __device__ __forceinline__ void end_unit(State&, const Params&) {}
+  static __device__ __forceinline__ void finish(const EpiCtx& cx) {
+    if (cx.lane == 0) tma_store_wait_all<0>();  // all dZ writes complete before the CTA (and its smem) goes away
+  }
 };
 
 // Plain GEMM epilogue: out[row, col] (+)= acc, bf16 or fp32 row-major.
 template <bool kF32>
 struct StoreEpi {
+  static constexpr uint32_t kSmemBytes = 0;
   struct Params {
     void* out;
     int rows, cols, ld, accumulate;
@@ -215,7 +257,7 @@ struct StoreEpi {
     st.row = row;
   }
   template <int BN>
-  static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0) {
+  static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0, const EpiCtx&) {
 #pragma unroll 1
     for (int c = 0; c < BN / 32; ++c) {
       const int col0 = n0 + c * 32;
@@ -265,24 +307,27 @@ struct StoreEpi {
   }
   template <int BN>
   static __device__ __forceinline__ void end_unit(State&, const Params&) {}
+  static __device__ __forceinline__ void finish(const EpiCtx&) {}
 };
 
 // ------------------------------------------------------------------------------------------------ the kernel
-template <int kCG, int BN, int kStages>
+template <int kCG, int BN, int kStages, uint32_t kEpiBytes>
 struct SmemLayout {
   static constexpr int LOAD_BN = BN / kCG;
   static constexpr uint32_t A_BYTES = BM * BK * 2;
   static constexpr uint32_t B_BYTES = LOAD_BN * BK * 2;
   static constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr uint32_t BAR_OFF = kStages * STAGE_BYTES;
+  static constexpr uint32_t EPI_OFF = kStages * STAGE_BYTES;  // 1024-byte aligned (stages are multiples of 1024)
+  static constexpr uint32_t BAR_OFF = EPI_OFF + kEpiBytes;
   static constexpr uint32_t BYTES = 1024 /*alignment slack*/ + BAR_OFF + (2 * kStages + 2 * kAccStages) * 8 + 16;
+  static_assert(BYTES <= 232448, "exceeds the 227 KB of shared memory a CTA can have");
 };
 
 template <int kCG, int BN, int kStages, bool kAMN, bool kBMN, class Epi>
 __global__ void __launch_bounds__(kThreads, 1)
     umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Sched sc,
-                const typename Epi::Params ep) {
-  using L = SmemLayout<kCG, BN, kStages>;
+                const __grid_constant__ typename Epi::Params ep) {
+  using L = SmemLayout<kCG, BN, kStages, Epi::kSmemBytes>;
   constexpr int LOAD_BN = L::LOAD_BN;
   static_assert(BN % 32 == 0 && BN <= 256 && kAccStages * BN <= kTmemCols, "accumulator does not fit TMEM");
   static_assert(LOAD_BN % 64 == 0, "B tile must be whole 64-wide swizzle atoms");
@@ -441,7 +486,8 @@ __global__ void __launch_bounds__(kThreads, 1)
     // ============================== epilogue ==============================
     const int q = warp & 3;  // TMEM lane quarter this warp may access
     const int row_in_tile = q * 32 + lane;
-    typename Epi::State st;
+    const EpiCtx cx{smem + L::EPI_OFF, q, lane};
+    typename Epi::State st = {};
     uint32_t it = 0;
     for (int u = cl; u < sc.n_units; u += n_cl) {
       int m_blk, chunk;
@@ -455,7 +501,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         mbar_wait(&tfull[as], aphase);
         tc_fence_after();
         const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + as * BN;
-        Epi::template tile<BN>(st, ep, taddr, nt * BN);
+        Epi::template tile<BN>(st, ep, taddr, nt * BN, cx);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
@@ -467,6 +513,7 @@ __global__ void __launch_bounds__(kThreads, 1)
       }
       Epi::template end_unit<BN>(st, ep);
     }
+    Epi::finish(cx);
   }
 
   // ---- teardown: nobody may leave while a peer can still touch its smem / barriers / TMEM
@@ -602,8 +649,15 @@ int make_tmap(CUtensorMap* tm, const void* base, uint64_t dim0, uint64_t dim1, u
   const cuuint64_t strides[1] = {pitch_bytes};
   const cuuint32_t box[2] = {box0, box1};
   const cuuint32_t estr[2] = {1, 1};
+  CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
+  if (const char* e = getenv("FTK_L2_PROMO")) {  // experiment knob: 0 none, 1 64 B, 2 128 B, 3 256 B
+    const int v = atoi(e);
+    promo = v == 0 ? CU_TENSOR_MAP_L2_PROMOTION_NONE
+                   : v == 1 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
+                            : v == 2 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B : CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
+  }
   const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, promo,
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fail(FTK_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
   return FTK_OK;
@@ -612,7 +666,7 @@ int make_tmap(CUtensorMap* tm, const void* base, uint64_t dim0, uint64_t dim1, u
 template <int kCG, int BN, int kStages, bool kAMN, bool kBMN, class Epi>
 int launch_umma(const CUtensorMap& tmA, const CUtensorMap& tmB, const Sched& sc, const typename Epi::Params& ep,
                 int sm_count, cudaStream_t st) {
-  using L = SmemLayout<kCG, BN, kStages>;
+  using L = SmemLayout<kCG, BN, kStages, Epi::kSmemBytes>;
   auto kern = umma_kernel<kCG, BN, kStages, kAMN, kBMN, Epi>;
   static bool attr_done[64] = {false};  // per instantiation and device
   int dev = 0;
@@ -669,6 +723,15 @@ void plan_chunks(int n_mblk, int n_ntile, int n_groups, int* n_chunks, int* tile
   *n_chunks = ceil_div(n_ntile, *tiles_per_chunk);
 }
 
+// m blocks per scheduling group: as many as keep the group's A blocks (rows x K bf16) within ~24 MB of L2.
+int pick_m_group(int n_mblk, int rows_per_mblk, int k_elems) {
+  const int64_t blk_bytes = static_cast<int64_t>(rows_per_mblk) * k_elems * 2;
+  int64_t g = (int64_t(24) << 20) / (blk_bytes > 0 ? blk_bytes : 1);
+  if (g < 1) g = 1;
+  if (g > n_mblk) g = n_mblk;
+  return static_cast<int>(g);
+}
+
 struct FwdWorkspace {
   float* pmax;
   float* psum;
@@ -717,8 +780,9 @@ int run_fwd(const void* H, const void* W, const void* bias, const int64_t* targe
   int n_chunks;
   plan_chunks(n_mblk, sc.n_ntile, sm_count / kCG, &n_chunks, &sc.tiles_per_chunk);
   sc.n_units = n_mblk * n_chunks;
-  sc.n_inner = n_mblk;
-  sc.inner_is_m = 1;
+  sc.n_mblk = n_mblk;
+  sc.n_chunks = n_chunks;
+  sc.m_group = pick_m_group(n_mblk, BM * kCG, d);
   sc.n_kblk = ceil_div(d, BK);
   FwdEpi::Params ep;
   ep.targets = targets;
@@ -762,14 +826,15 @@ int run_bwd_slab(const void* H, const void* W, const void* bias, const int64_t* 
     int n_chunks;
     plan_chunks(n_mblk, sc.n_ntile, n_groups, &n_chunks, &sc.tiles_per_chunk);
     sc.n_units = n_mblk * n_chunks;
-    sc.n_inner = n_mblk;
-    sc.inner_is_m = 1;
+    sc.n_mblk = n_mblk;
+    sc.n_chunks = n_chunks;
+    sc.m_group = pick_m_group(n_mblk, BM * kCG, d);
     sc.n_kblk = ceil_div(d, BK);
     DzEpi::Params ep;
     ep.targets = targets;
     ep.bias = static_cast<const __nv_bfloat16*>(bias);
     ep.lse = lse;
-    ep.dz = dz;
+    if (int rc = make_tmap(&ep.tm_out, dz, ld, rows, static_cast<uint64_t>(ld) * 2, 64, 32)) return rc;
     ep.scale_dev = grad_scale_dev;
     ep.nvalid_dev = n_valid_dev;
     ep.scale = grad_scale;
@@ -788,8 +853,9 @@ int run_bwd_slab(const void* H, const void* W, const void* bias, const int64_t* 
     sc.n_ntile = ceil_div(d, BN);
     sc.tiles_per_chunk = 1;
     sc.n_units = n_mblk * sc.n_ntile;
-    sc.n_inner = sc.n_ntile;  // N tiles of one m block are adjacent: the dZ rows are read from HBM once
-    sc.inner_is_m = 0;
+    sc.n_mblk = n_mblk;
+    sc.n_chunks = sc.n_ntile;
+    sc.m_group = 1;  // N tiles of one m block are adjacent: the dZ rows are read from HBM once
     sc.n_kblk = ceil_div(V, BK);
     StoreEpi<false>::Params ep;
     ep.out = dH;
@@ -809,8 +875,9 @@ int run_bwd_slab(const void* H, const void* W, const void* bias, const int64_t* 
     sc.n_ntile = ceil_div(d, BN);
     sc.tiles_per_chunk = 1;
     sc.n_units = n_mblk * sc.n_ntile;
-    sc.n_inner = sc.n_ntile;
-    sc.inner_is_m = 0;
+    sc.n_mblk = n_mblk;
+    sc.n_chunks = sc.n_ntile;
+    sc.m_group = 1;
     sc.n_kblk = ceil_div(rows, BK);
     if (dw_dtype == FTK_F32) {
       StoreEpi<true>::Params ep;
