@@ -164,6 +164,30 @@ int ftk_dp_allreduce(ftk_dp_t* dp, void* buf, size_t count, int32_t dtype, float
 int ftk_dp_join(ftk_dp_t* dp, void* stream);
 int ftk_dp_destroy(ftk_dp_t* dp);
 
+/*
+ * Optimizer step on the device, consuming the reduced gradient buckets in place
+ * (next row of SURVEY.md 8f). Replaces the reference's DeepSpeed AdamW
+ * (finetuner/ds_config.json:10-18, weight_decay 0.01 from FT.py:992, CPU-offloaded
+ * by default at ds_config.json:35-40) and its gradient clipping
+ * (ds_config.json:44). Arithmetic of torch.optim.AdamW: decoupled weight decay,
+ * bias-corrected moments.
+ *
+ *   ftk_grad_sqnorm  out[0] (+)= sum g^2 over n elements (FTK_BF16 / FTK_F32), reduced in a
+ *                    fixed order (deterministic); workspace from ftk_grad_sqnorm_workspace()
+ *   ftk_clip_coef    coef[0] = min(1, max_norm / (sqrt(sqnorm[0]) + 1e-6))  (clip_grad_norm_)
+ *   ftk_adamw_step   one AdamW update of n elements; step counts from 1.
+ *                    param FTK_F32: updated in place (grad FTK_F32 or FTK_BF16, master unused);
+ *                    param FTK_BF16: `master` (fp32) is updated and param is its bf16 rounding.
+ *                    Every gradient is first multiplied by grad_scale * (grad_scale_dev ? *grad_scale_dev : 1).
+ */
+size_t ftk_grad_sqnorm_workspace(void);
+int ftk_grad_sqnorm(const void* grad, size_t n, int32_t dtype, float* out, int32_t accumulate, void* workspace,
+                    size_t workspace_bytes, void* stream);
+int ftk_clip_coef(const float* sqnorm, float max_norm, float* coef, void* stream);
+int ftk_adamw_step(void* param, const void* grad, float* master, float* exp_avg, float* exp_avg_sq, size_t n,
+                   int32_t param_dtype, int32_t grad_dtype, float lr, float beta1, float beta2, float eps,
+                   float weight_decay, int64_t step, float grad_scale, const float* grad_scale_dev, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

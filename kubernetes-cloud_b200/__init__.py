@@ -11,7 +11,8 @@ from . import _lib  # noqa: F401
 from ._lib import FtkError, build  # noqa: F401
 
 __all__ = ["FtkError", "build", "TokenizedDataset", "collector", "DeviceCollator", "compute_loss",
-           "ModifiedTrainerMixin", "fused_lmhead_ce", "train_order", "rank_slice", "GradSync"]
+           "ModifiedTrainerMixin", "fused_lmhead_ce", "train_order", "rank_slice", "GradSync", "FusedAdamW", "WarmupLR",
+           "DeviceBatcher", "write_token_file", "validate_token_file"]
 
 
 def __getattr__(name):  # lazy: importing the package must not need torch.cuda or the .so
@@ -30,4 +31,13 @@ def __getattr__(name):  # lazy: importing the package must not need torch.cuda o
     if name in ("GradSync",):
         from . import dp
         return getattr(dp, name)
+    if name in ("FusedAdamW", "WarmupLR"):
+        from . import optim
+        return getattr(optim, name)
+    if name in ("DeviceBatcher",):
+        from . import pipeline
+        return getattr(pipeline, name)
+    if name in ("write_token_file", "validate_token_file", "TokenFileReport"):
+        from . import tokenfile
+        return getattr(tokenfile, name)
     raise AttributeError(name)

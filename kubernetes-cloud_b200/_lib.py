@@ -36,6 +36,11 @@ SIGNATURES = {
     "ftk_dp_allreduce": (c_int32, [c_void_p, c_void_p, c_size_t, c_int32, c_float, c_void_p]),
     "ftk_dp_join": (c_int32, [c_void_p, c_void_p]),
     "ftk_dp_destroy": (c_int32, [c_void_p]),
+    "ftk_grad_sqnorm_workspace": (c_size_t, []),
+    "ftk_grad_sqnorm": (c_int32, [c_void_p, c_size_t, c_int32, c_void_p, c_int32, c_void_p, c_size_t, c_void_p]),
+    "ftk_clip_coef": (c_int32, [c_void_p, c_float, c_void_p, c_void_p]),
+    "ftk_adamw_step": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int32, c_int32, c_float,
+                                 c_float, c_float, c_float, c_float, c_int64, c_float, c_void_p, c_void_p]),
 }
 
 

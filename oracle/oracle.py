@@ -189,3 +189,36 @@ def rel_err(a: torch.Tensor, b: torch.Tensor) -> float:
     b = b.detach().to("cpu", torch.float64)
     den = float(b.norm())
     return float((a - b).norm()) / (den if den > 0 else 1.0)
+
+
+# ---------------------------------------------------------------------------------------------- optimizer (8f rank 1)
+def warmup_lr_reference(it: int, max_lr: float, warmup_steps: int, min_lr: float = 0.0, warmup_type: str = "log") -> float:
+    """DeepSpeed 0.9.2 ``runtime/lr_schedules.py`` WarmupLR (third-party, absent from /root/reference; named by the
+    reference at finetuner/ds_config.json:19-26): gamma = log(it + 1) / log(warmup_steps) ("log") or
+    it / warmup_steps ("linear") during warm-up, 1 afterwards; lr = min + (max - min) * gamma."""
+    import math
+    warmup_steps = max(2, warmup_steps)
+    if it < warmup_steps:
+        gamma = math.log(it + 1) / math.log(warmup_steps) if warmup_type == "log" else it / warmup_steps
+    else:
+        gamma = 1.0
+    return min_lr + (max_lr - min_lr) * gamma
+
+
+def adamw_reference(params, grads_per_step, lrs, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.01, max_grad_norm=1.0):
+    """torch.optim.AdamW + torch.nn.utils.clip_grad_norm_ on CPU fp32 (what HF/DeepSpeed apply for the reference:
+    ds_config.json:10-18 AdamW, :44 gradient_clipping; FT.py:992 weight_decay 0.01).
+    params: list of tensors; grads_per_step: list (per step) of lists of tensors; lrs: lr per step.
+    Returns the updated parameters (fp32) and the pre-clip global norms."""
+    ps = [torch.nn.Parameter(p.detach().to("cpu", torch.float32).clone()) for p in params]
+    opt = torch.optim.AdamW(ps, lr=lrs[0], betas=betas, eps=eps, weight_decay=weight_decay)
+    norms = []
+    for lr, grads in zip(lrs, grads_per_step):
+        for g in opt.param_groups:
+            g["lr"] = lr
+        for p, gr in zip(ps, grads):
+            p.grad = gr.detach().to("cpu", torch.float32).clone()
+        if max_grad_norm is not None:
+            norms.append(float(torch.nn.utils.clip_grad_norm_(ps, max_grad_norm)))
+        opt.step()
+    return [p.detach() for p in ps], norms

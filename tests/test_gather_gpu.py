@@ -88,3 +88,31 @@ def test_bulk_properties(cuda_dev):
     assert torch.equal(mask, ids != 50256)
     assert torch.equal(labels, torch.where(mask, ids, torch.full_like(ids, -100)))
     assert torch.equal(n_valid.to(torch.int64), mask.sum(1))
+
+
+def test_device_batcher_epoch_matches_reference_order(cuda_dev, tmp_path):
+    """The pipeline yields exactly the batches the reference would: random_split order, rank slice, resume."""
+    from kubernetes_cloud_b200 import DeviceBatcher, TokenizedDataset, write_token_file
+    T, n = 64, 21
+    toks = np.random.default_rng(3).integers(0, 500, size=n * T - 5)
+    path = str(tmp_path / "t.tokens")
+    write_token_file(path, toks, T, pad_id=500)
+    raw = np.fromfile(path, dtype=np.uint16)
+    ds = TokenizedDataset(path, T, pad_token_id=500, eos_token_id=500)
+    for rank, world in ((0, 1), (1, 2)):
+        order = O.rank_slice(O.train_order(n, 42, True), rank, world)
+        bt = DeviceBatcher(ds, batch_size=4, seed=42, shuffle=True, rank=rank, world=world, shift_labels=True, prefetch=3)
+        got = list(bt.epoch())
+        assert len(got) == bt.batches_per_epoch() == (len(order) + 3) // 4
+        for k, b in enumerate(got):
+            idx = order[4 * k:4 * k + 4]
+            np.testing.assert_array_equal(bt.index_list(k).numpy(), idx)
+            want = O.gather_c(raw, T, idx, 500, True, True)
+            np.testing.assert_array_equal(b["input_ids"].cpu().numpy(), want[0])
+            np.testing.assert_array_equal(b["labels"].cpu().numpy(), want[1])
+            np.testing.assert_array_equal(b["attention_mask"].cpu().numpy(), want[2])
+        resumed = list(bt.epoch(start_batch=2))
+        assert len(resumed) == len(got) - 2
+        assert torch.equal(resumed[0]["input_ids"], got[2]["input_ids"])
+    ns = DeviceBatcher(ds, batch_size=8, shuffle=False)  # --no-shuffle keeps file order
+    np.testing.assert_array_equal(ns.index_list(0).numpy(), np.arange(8))

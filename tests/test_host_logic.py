@@ -97,3 +97,44 @@ def test_grad_sync_rejects_cpu_params_for_ftk_backend():
     from kubernetes_cloud_b200.dp import GradSync
     with pytest.raises(FtkError):
         GradSync(torch.nn.Linear(4, 4).parameters(), 0, 1, backend="ftk")
+
+
+def test_warmup_lr_matches_deepspeed_formula():
+    from kubernetes_cloud_b200.optim import WarmupLR
+    for typ in ("log", "linear"):
+        s = WarmupLR(max_lr=5e-5, warmup_steps=10, min_lr=1e-6, warmup_type=typ)
+        for it in range(0, 25):
+            assert abs(s.lr_at(it) - O.warmup_lr_reference(it, 5e-5, 10, 1e-6, typ)) < 1e-18
+        assert s.lr_at(0) == pytest.approx(1e-6) and s.lr_at(10) == pytest.approx(5e-5) and s.lr_at(1000) == pytest.approx(5e-5)
+    with pytest.raises(ValueError):
+        WarmupLR(1e-3, 10, warmup_type="cosine")
+
+
+def test_token_file_writer_and_validator(tmp_path):
+    from kubernetes_cloud_b200 import validate_token_file, write_token_file
+    T = 32
+    rng = np.random.default_rng(0)
+    toks = rng.integers(0, 1000, size=5 * T - 7)
+    p = str(tmp_path / "a.tokens")
+    assert write_token_file(p, toks, T, pad_id=1000) == 5
+    raw = np.fromfile(p, dtype=np.uint16)
+    assert raw.size == 5 * T and (raw[-7:] == 1000).all() and (raw[:toks.size] == toks).all()
+    rep = validate_token_file(p, T, vocab_size=1001, pad_id=1000, eos_id=1000)
+    assert rep.ok and rep.n_contexts == 5 and rep.trailing_bytes == 0 and rep.max_token == 1000
+    assert rep.padded_contexts == [4] and rep.convention_ok is True and rep.vocab_ok is True
+    # the oracle's reader agrees with what was written (same format the reference reads)
+    ids, labels, mask, _ = O.gather_numpy(raw, T, [4], 1000, True)
+    assert mask[0].sum() == T - 7 and (labels[0, -7:] == -100).all()
+    # violations: vocabulary, trailing partial context, padding in a non-final context when pad == eos
+    assert not validate_token_file(p, T, vocab_size=1000).ok
+    with open(p, "ab") as f:
+        f.write(b"\x00" * 6)
+    rep = validate_token_file(p, T)
+    assert rep.trailing_bytes == 6 and rep.n_contexts == 5 and not rep.ok
+    raw[2 * T - 3:2 * T] = 1000
+    raw.tofile(p)
+    rep = validate_token_file(p, T, pad_id=1000, eos_id=1000)
+    assert rep.convention_ok is False and rep.padded_contexts == [1, 4]
+    assert validate_token_file(p, T, pad_id=1000, eos_id=999).ok  # distinct pad: every context is masked by id
+    with pytest.raises(ValueError):
+        write_token_file(p, [70000], T, 0)

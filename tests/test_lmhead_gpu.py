@@ -140,3 +140,36 @@ def test_full_size_properties(cuda_dev):
     p[~ok] = 0
     dH_ref = (p / float(n_valid)) @ W.float()
     assert O.rel_err(dH1[rows].float(), dH_ref) < GRAD_RTOL
+
+
+def test_compute_loss_dropin_against_hf_model(cuda_dev):
+    """The reference-facing surface: compute_loss(model, inputs) with an HF GPT-Neo (BASELINE configs[0] architecture,
+    scaled down) must give HF's own loss and lm_head gradient.  Same bf16 trunk on both sides, so the comparison
+    isolates lm_head + loss; HF rounds its logits to bf16 before the upcast, hence the slightly looser tolerance."""
+    from transformers import GPTNeoConfig, GPTNeoForCausalLM
+    from kubernetes_cloud_b200.loss import compute_loss
+    torch.manual_seed(42)
+    cfg = GPTNeoConfig(vocab_size=50257, hidden_size=128, num_layers=2, num_heads=4, max_position_embeddings=256,
+                       attention_types=[[["global", "local"], 1]], window_size=64)
+    model = GPTNeoForCausalLM(cfg).cuda().to(torch.bfloat16)
+    model.train()
+    B, T = 2, 256
+    tok = O.synth_tokens(4, T, 50257, 1234, trailing_pads=40)
+    ids, _, mask, _ = O.gather_numpy(tok, T, [3, 1], 50256, True)
+    inputs = {"input_ids": torch.from_numpy(ids).cuda(), "attention_mask": torch.from_numpy(mask).cuda(),
+              "labels": torch.from_numpy(ids).cuda()}  # what collector produces: labels = unmasked copy of ids
+    # HF's own path (what super().compute_loss does in the reference, FT.py:479)
+    ref_labels = inputs["labels"].clone().masked_fill_(~inputs["attention_mask"], -100)
+    model.zero_grad()
+    ref = model(input_ids=inputs["input_ids"], attention_mask=inputs["attention_mask"], labels=ref_labels).loss
+    ref.backward()
+    ref_grad = model.lm_head.weight.grad.detach().float().clone()
+    # the drop-in
+    model.zero_grad()
+    loss = compute_loss(model, inputs)
+    assert loss.requires_grad and loss.dim() == 0
+    assert torch.equal(inputs["labels"], ref_labels)  # labels filled in place, as FT.py:476-477 does
+    loss.backward()
+    got_grad = model.lm_head.weight.grad.detach().float()
+    assert abs(float(loss) - float(ref)) <= 3e-3 * abs(float(ref))
+    assert O.rel_err(got_grad, ref_grad) < 3e-2  # tied weights: includes the embedding's share, identical on both sides
