@@ -30,6 +30,7 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
+RESULT_OUT = sys.stdout  # replaced by a private handle on the real stdout in __main__
 
 D_MODEL, VOCAB, CTX, BATCH = 2048, 50257, 2048, 8  # GPT-Neo-1.3B head (GPTNeoConfig defaults), 8 contexts / GPU
 N_CTX_FILE = 4096                                   # contexts in the synthetic token stream
@@ -175,7 +176,7 @@ def main_reference(args) -> None:
                              "sample": f"{args.steps} steps of 1 context (2048 tokens)", "host_cpus": os.cpu_count()},
             "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=RESULT_OUT, flush=True)
 
 
 # ------------------------------------------------------------------------------------------------ GPU arm
@@ -192,8 +193,11 @@ def main_gpu(args) -> None:
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    sm_reserve = int(os.environ.get("FTK_BENCH_SM_RESERVE", "0")) if world > 1 else 0  # measured: no gain
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if sm_reserve:
+            os.environ.setdefault("NCCL_MAX_CTAS", str(sm_reserve))  # the all-reduce must fit the reserved SMs
         dist.init_process_group("nccl", device_id=dev)
     L = _lib.lib()
 
@@ -232,7 +236,11 @@ def main_gpu(args) -> None:
         ids, targets, mask, n_valid_rows = torch.ops.ftk.gather_windows(tok, idx, CTX, PAD_ID, True, True)
         if timed:
             e0 = torch.cuda.Event(enable_timing=True); e0.record(stream); ev_f0.append(e0)
+        if sm_reserve and state["dW"] is not None:
+            L.ftk_set_sm_reserve(sm_reserve)  # the previous step's all-reduce runs beside this forward
         loss_sum, n_valid, lse = torch.ops.ftk.lmhead_ce_fwd(hidden, W, None, targets.view(-1))
+        if sm_reserve:
+            L.ftk_set_sm_reserve(0)
         if timed:
             e1 = torch.cuda.Event(enable_timing=True); e1.record(stream); ev_f1.append(e1)
         if handle is not None and state["dW"] is not None:
@@ -402,7 +410,8 @@ def main_gpu(args) -> None:
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
         "config": {"workload": WORKLOAD, "tokens_per_gpu_per_step": M, "parallelism": f"dp{world}",
                    "l2": "inputs (W 206 MB + H 67 MB) larger than the 126 MB L2; no explicit flush",
-                   "grad_sync": "all-reduce of dW (103M bf16) / world on the comm stream" if world > 1 else "none (1 GPU)"},
+                   "grad_sync": (f"all-reduce of dW (103M bf16) / world on the comm stream, issued behind the backward and "
+                                 f"joined before the next one ({sm_reserve} SMs reserved for NCCL)") if world > 1 else "none (1 GPU)"},
         "tokens_per_s_per_gpu": value / world,
         "loss": loss_val,
         "roofline": {"bound": "tensor", "kernel": "umma_kernel<FwdEpi> (fused lm_head GEMM + online-softmax CE)",
@@ -432,12 +441,22 @@ def main_gpu(args) -> None:
     }
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = run_cpu_baseline()
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=RESULT_OUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
+def _claim_stdout():
+    """Libraries loaded later (NCCL prints its version banner) write to fd 1; the contract is ONE JSON line on stdout.
+    Point fd 1 at stderr for everything else and keep a private handle on the real stdout for the result line."""
+    real = os.fdopen(os.dup(1), "w")
+    sys.stdout.flush()
+    os.dup2(2, 1)
+    return real
+
+
 if __name__ == "__main__":
+    RESULT_OUT = _claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=50)

@@ -156,7 +156,13 @@ int ftk_lmhead_ce_bwd(const void* H, const void* W, const void* bias, const int6
  *                     multiply by prescale (1/world for the reference's mean), ncclAllReduce(sum)
  *                     in place over `count` elements of dtype (FTK_BF16/FTK_F32); never blocks the host
  *   ftk_dp_join       makes `stream` wait for everything issued on the comm stream so far
+ *   ftk_set_sm_reserve  process-wide: the persistent lm_head kernels launched after this call leave n_sms SMs
+ *                     idle (0 = use all). A NCCL kernel cannot share an SM with them, so without a reserve an
+ *                     all-reduce issued on the comm stream only starts when the running GEMM ends; with one
+ *                     (and NCCL_MAX_CTAS <= n_sms) it overlaps. Host-serial callers toggle it around the
+ *                     kernels that should overlap.
  */
+int ftk_set_sm_reserve(int32_t n_sms);
 typedef struct ftk_dp ftk_dp_t;
 int ftk_dp_unique_id(void* id128_host);
 int ftk_dp_init(const void* id128_host, int32_t rank, int32_t world, ftk_dp_t** out);

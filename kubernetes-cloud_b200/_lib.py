@@ -31,6 +31,7 @@ SIGNATURES = {
     "ftk_lmhead_ce_bwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32,
                                     c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_void_p,
                                     c_void_p, c_size_t, c_void_p]),
+    "ftk_set_sm_reserve": (c_int32, [c_int32]),
     "ftk_dp_unique_id": (c_int32, [c_void_p]),
     "ftk_dp_init": (c_int32, [c_void_p, c_int32, c_int32, POINTER(c_void_p)]),
     "ftk_dp_allreduce": (c_int32, [c_void_p, c_void_p, c_size_t, c_int32, c_float, c_void_p]),

@@ -663,6 +663,10 @@ int make_tmap(CUtensorMap* tm, const void* base, uint64_t dim0, uint64_t dim1, u
   return FTK_OK;
 }
 
+// SMs the persistent kernels leave idle (ftk_set_sm_reserve): room for a concurrent NCCL kernel, whose CTAs cannot
+// share an SM with ours (registers) and would otherwise wait for a whole GEMM to finish.
+int g_sm_reserve = 0;
+
 template <int kCG, int BN, int kStages, bool kAMN, bool kBMN, class Epi>
 int launch_umma(const CUtensorMap& tmA, const CUtensorMap& tmB, const Sched& sc, const typename Epi::Params& ep,
                 int sm_count, cudaStream_t st) {
@@ -675,7 +679,9 @@ int launch_umma(const CUtensorMap& tmA, const CUtensorMap& tmB, const Sched& sc,
     FTK_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(L::BYTES)));
     attr_done[dev & 63] = true;
   }
-  int n_cl = sm_count / kCG;
+  int usable = sm_count - g_sm_reserve;
+  if (usable < kCG) usable = kCG;
+  int n_cl = usable / kCG;
   if (n_cl > sc.n_units) n_cl = sc.n_units;
   if (n_cl <= 0) return FTK_OK;
   cudaLaunchConfig_t cfg = {};
@@ -778,7 +784,8 @@ int run_fwd(const void* H, const void* W, const void* bias, const int64_t* targe
   const int n_mblk = ceil_div(M, BM * kCG);
   sc.n_ntile = ceil_div(V, BN);
   int n_chunks;
-  plan_chunks(n_mblk, sc.n_ntile, sm_count / kCG, &n_chunks, &sc.tiles_per_chunk);
+  plan_chunks(n_mblk, sc.n_ntile, (sm_count - g_sm_reserve > kCG ? sm_count - g_sm_reserve : kCG) / kCG, &n_chunks,
+              &sc.tiles_per_chunk);
   sc.n_units = n_mblk * n_chunks;
   sc.n_mblk = n_mblk;
   sc.n_chunks = n_chunks;
@@ -921,6 +928,12 @@ int check_common(const void* H, const void* W, int64_t M, int d, int V, ftk::Dev
 }
 
 }  // namespace
+
+extern "C" int ftk_set_sm_reserve(int32_t n_sms) {
+  FTK_REQUIRE(n_sms >= 0 && n_sms <= 64, "ftk_set_sm_reserve: %d out of range [0, 64]", n_sms);
+  g_sm_reserve = n_sms;
+  return FTK_OK;
+}
 
 extern "C" size_t ftk_lmhead_ce_fwd_workspace(int64_t M, int32_t d, int32_t V) {
   (void)d;
