@@ -6,6 +6,7 @@
 // library itself has no link-time dependency on it and loads on machines without NCCL.
 #include <cuda_bf16.h>
 #include <dlfcn.h>
+#include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
@@ -19,7 +20,8 @@ typedef struct {
   char internal[128];
 } ncclUniqueId;
 typedef int ncclResult_t;
-enum { ncclSum = 0 };
+enum { ncclSum = 0, ncclAvg = 4 };
+enum { ncclScalarHostImmediate = 1 };
 enum { ncclFloat32 = 7, ncclBfloat16 = 9 };
 
 struct NcclApi {
@@ -28,6 +30,8 @@ struct NcclApi {
   ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int);
   ncclResult_t (*CommDestroy)(ncclComm_t);
   ncclResult_t (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t);
+  ncclResult_t (*RedOpCreatePreMulSum)(int*, void*, int, int, ncclComm_t);  // optional (NCCL >= 2.11)
+  ncclResult_t (*RedOpDestroy)(int, ncclComm_t);
   const char* (*GetErrorString)(ncclResult_t);
 };
 
@@ -47,6 +51,9 @@ int load_nccl(NcclApi** out) {
     api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(dlsym(h, "ncclCommDestroy"));
     api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(dlsym(h, "ncclAllReduce"));
     api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(dlsym(h, "ncclGetErrorString"));
+    api.RedOpCreatePreMulSum =
+        reinterpret_cast<decltype(api.RedOpCreatePreMulSum)>(dlsym(h, "ncclRedOpCreatePreMulSum"));
+    api.RedOpDestroy = reinterpret_cast<decltype(api.RedOpDestroy)>(dlsym(h, "ncclRedOpDestroy"));
     if (!api.GetUniqueId || !api.CommInitRank || !api.CommDestroy || !api.AllReduce || !api.GetErrorString)
       return ftk::fail(FTK_ENCCL, "NCCL library lacks a required symbol");
     loaded = true;
@@ -112,6 +119,22 @@ struct ftk_dp {
   int rank, world, sm_count;
 };
 
+static int launch_prescale(ftk_dp* dp, void* buf, size_t count, int32_t dtype, float prescale) {
+  const size_t vec = count / (dtype == FTK_F32 ? 4 : 8);
+  size_t blocks = (vec + 255) / 256;
+  const size_t cap = static_cast<size_t>(dp->sm_count) * 8;
+  if (blocks > cap) blocks = cap;
+  if (blocks == 0) blocks = 1;
+  if (dtype == FTK_F32)
+    prescale_kernel<float><<<static_cast<unsigned>(blocks), 256, 0, dp->comm_stream>>>(static_cast<float*>(buf), count,
+                                                                                     prescale);
+  else
+    prescale_kernel<__nv_bfloat16><<<static_cast<unsigned>(blocks), 256, 0, dp->comm_stream>>>(
+        static_cast<__nv_bfloat16*>(buf), count, prescale);
+  FTK_CUDA_CHECK(cudaGetLastError());
+  return FTK_OK;
+}
+
 extern "C" int ftk_dp_unique_id(void* id128_host) {
   FTK_REQUIRE(id128_host != nullptr, "ftk_dp_unique_id: null output");
   NcclApi* api;
@@ -159,23 +182,30 @@ extern "C" int ftk_dp_allreduce(ftk_dp_t* dp, void* buf, size_t count, int32_t d
   // the bucket is ready once everything issued so far on ready_stream has run
   FTK_CUDA_CHECK(cudaEventRecord(dp->ev_ready, static_cast<cudaStream_t>(ready_stream)));
   FTK_CUDA_CHECK(cudaStreamWaitEvent(dp->comm_stream, dp->ev_ready, 0));
-  if (prescale != 1.0f) {
-    const size_t vec = count / (dtype == FTK_F32 ? 4 : 8);
-    size_t blocks = (vec + 255) / 256;
-    const size_t cap = static_cast<size_t>(dp->sm_count) * 8;
-    if (blocks > cap) blocks = cap;
-    if (blocks == 0) blocks = 1;
-    if (dtype == FTK_F32)
-      prescale_kernel<float><<<static_cast<unsigned>(blocks), 256, 0, dp->comm_stream>>>(static_cast<float*>(buf),
-                                                                                       count, prescale);
-    else
-      prescale_kernel<__nv_bfloat16><<<static_cast<unsigned>(blocks), 256, 0, dp->comm_stream>>>(
-          static_cast<__nv_bfloat16*>(buf), count, prescale);
-    FTK_CUDA_CHECK(cudaGetLastError());
-  }
+  // The scale is folded into the collective (ncclAvg for 1/world, a pre-multiplied sum otherwise): a separate
+  // scaling kernel on the comm stream would have to squeeze through whatever SMs a concurrent persistent GEMM left
+  // free and delays the all-reduce by about a millisecond (profiles/r01_overlap_probe.txt).
+  const int nccl_dt = dtype == FTK_F32 ? ncclFloat32 : ncclBfloat16;
   if (dp->world > 1) {
-    FTK_NCCL_CHECK(dp->api, dp->api->AllReduce(buf, buf, count, dtype == FTK_F32 ? ncclFloat32 : ncclBfloat16, ncclSum,
-                                               dp->comm, dp->comm_stream));
+    const float avg = 1.0f / static_cast<float>(dp->world);
+    if (prescale == 1.0f) {
+      FTK_NCCL_CHECK(dp->api, dp->api->AllReduce(buf, buf, count, nccl_dt, ncclSum, dp->comm, dp->comm_stream));
+    } else if (fabsf(prescale - avg) <= 1e-7f * avg) {
+      FTK_NCCL_CHECK(dp->api, dp->api->AllReduce(buf, buf, count, nccl_dt, ncclAvg, dp->comm, dp->comm_stream));
+    } else if (dp->api->RedOpCreatePreMulSum != nullptr && dp->api->RedOpDestroy != nullptr) {
+      int op = 0;
+      float s32 = prescale;
+      __nv_bfloat16 s16 = __float2bfloat16(prescale);
+      void* scalar = dtype == FTK_F32 ? static_cast<void*>(&s32) : static_cast<void*>(&s16);
+      FTK_NCCL_CHECK(dp->api, dp->api->RedOpCreatePreMulSum(&op, scalar, nccl_dt, ncclScalarHostImmediate, dp->comm));
+      FTK_NCCL_CHECK(dp->api, dp->api->AllReduce(buf, buf, count, nccl_dt, op, dp->comm, dp->comm_stream));
+      FTK_NCCL_CHECK(dp->api, dp->api->RedOpDestroy(op, dp->comm));
+    } else {
+      if (int rc = launch_prescale(dp, buf, count, dtype, prescale)) return rc;
+      FTK_NCCL_CHECK(dp->api, dp->api->AllReduce(buf, buf, count, nccl_dt, ncclSum, dp->comm, dp->comm_stream));
+    }
+  } else if (prescale != 1.0f) {
+    if (int rc = launch_prescale(dp, buf, count, dtype, prescale)) return rc;  // world 1: only the scale remains
   }
   return FTK_OK;
 }
