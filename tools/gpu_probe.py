@@ -116,7 +116,18 @@ def stage_time():
 SMALL_F = [(128, 64, 256, False), (256, 128, 1000, False), (300, 64, 777, True), (2048, 768, 50257, False)]
 SMALL_B = [(128, 64, 256, False, 0), (256, 128, 1000, False, 0), (300, 64, 777, True, 0), (1024, 256, 5000, False, 256),
            (2048, 768, 50257, False, 0)]
+def stage_san():
+    """Small shapes for compute-sanitizer runs."""
+    r = {}
+    r.update(stage_fwd([(256, 128, 1000, False), (300, 64, 777, True)]))
+    r.update(stage_bwd([(256, 128, 1000, False, 0), (300, 64, 777, True, 0), (600, 64, 300, False, 256)]))
+    g = stage_gather()
+    r["gather_all_ok"] = all(g.values())
+    return r
+
+
 STAGES = {
+    "san": lambda: stage_san(),
     "gather": lambda: stage_gather(),
     "fwd": lambda: stage_fwd(SMALL_F),
     "bwd": lambda: stage_bwd(SMALL_B),
