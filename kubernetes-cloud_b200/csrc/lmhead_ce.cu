@@ -15,6 +15,7 @@
 #include <cuda.h>
 #include <math.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include "ftk_host.h"
 #include "ftk_ptx.cuh"
@@ -45,6 +46,8 @@ struct Sched {
   int tiles_per_chunk;  // N tiles per unit
   int n_ntile;          // N tiles in total
   int n_kblk;           // K blocks of BK
+  uint64_t hint_a;      // L2 eviction policy of the A / B operand loads
+  uint64_t hint_b;
 };
 
 __device__ __forceinline__ void decode_unit(const Sched& sc, int u, int& m_blk, int& chunk) {
@@ -159,6 +162,7 @@ struct DzEpi {
     const float* lse;           // [rows]
     const float* scale_dev;     // optional device scalar multiplied into scale
     const int32_t* nvalid_dev;  // optional device count divided out of scale
+    uint64_t store_hint;        // L2 eviction policy of the dZ stores
     float scale;
     int rows, V, ld;
   };
@@ -228,7 +232,8 @@ struct DzEpi {
       fence_async_shared();  // make the generic-proxy smem writes visible to the TMA engine
       __syncwarp();
       if (cx.lane == 0) {
-        tma_store_2d(&p.tm_out, buf, col0, row0);  // rows >= p.rows / columns >= ld are clipped by the tensor map
+        // rows >= p.rows / columns >= ld are clipped by the tensor map
+        tma_store_2d_hint(&p.tm_out, buf, col0, row0, p.store_hint);
         tma_store_commit();
       }
       ++st.nstore;
@@ -404,30 +409,30 @@ __global__ void __launch_bounds__(kThreads, 1)
             const int k0 = kb * BK;
             if constexpr (!kAMN) {
               if constexpr (kCG == 1)
-                tma_load_2d(a_dst, &tmA, bar, k0, m0);
+                tma_load_2d_hint(a_dst, &tmA, bar, k0, m0, sc.hint_a);
               else
-                tma_load_2d_pair(a_dst, &tmA, bar, k0, m0);
+                tma_load_2d_pair_hint(a_dst, &tmA, bar, k0, m0, sc.hint_a);
             } else {
 #pragma unroll
               for (int j = 0; j < BM / 64; ++j) {
                 if constexpr (kCG == 1)
-                  tma_load_2d(a_dst + j * (BK * 128), &tmA, bar, m0 + 64 * j, k0);
+                  tma_load_2d_hint(a_dst + j * (BK * 128), &tmA, bar, m0 + 64 * j, k0, sc.hint_a);
                 else
-                  tma_load_2d_pair(a_dst + j * (BK * 128), &tmA, bar, m0 + 64 * j, k0);
+                  tma_load_2d_pair_hint(a_dst + j * (BK * 128), &tmA, bar, m0 + 64 * j, k0, sc.hint_a);
               }
             }
             if constexpr (!kBMN) {
               if constexpr (kCG == 1)
-                tma_load_2d(b_dst, &tmB, bar, k0, n0);
+                tma_load_2d_hint(b_dst, &tmB, bar, k0, n0, sc.hint_b);
               else
-                tma_load_2d_pair(b_dst, &tmB, bar, k0, n0);
+                tma_load_2d_pair_hint(b_dst, &tmB, bar, k0, n0, sc.hint_b);
             } else {
 #pragma unroll
               for (int j = 0; j < LOAD_BN / 64; ++j) {
                 if constexpr (kCG == 1)
-                  tma_load_2d(b_dst + j * (BK * 128), &tmB, bar, n0 + 64 * j, k0);
+                  tma_load_2d_hint(b_dst + j * (BK * 128), &tmB, bar, n0 + 64 * j, k0, sc.hint_b);
                 else
-                  tma_load_2d_pair(b_dst + j * (BK * 128), &tmB, bar, n0 + 64 * j, k0);
+                  tma_load_2d_pair_hint(b_dst + j * (BK * 128), &tmB, bar, n0 + 64 * j, k0, sc.hint_b);
               }
             }
             if (++stage == kStages) {
@@ -729,6 +734,17 @@ void plan_chunks(int n_mblk, int n_ntile, int n_groups, int* n_chunks, int* tile
   *n_chunks = ceil_div(n_ntile, *tiles_per_chunk);
 }
 
+// L2 eviction policy per operand role; FTK_HINTS="<a><b><s>" with letters n/f/l overrides (experiments).
+uint64_t hint_of(char c) { return c == 'f' ? kEvictFirst : c == 'l' ? kEvictLast : kEvictNormal; }
+void pick_hints(const char* kernel_defaults, int kernel_idx, uint64_t* a, uint64_t* b, uint64_t* s) {
+  // kernel_idx: 0 fwd, 1 dz, 2 dH, 3 dW; FTK_HINTS holds 3 letters per kernel, 12 in all
+  const char* e = getenv("FTK_HINTS");
+  const char* src = (e != nullptr && strlen(e) >= 12) ? e + 3 * kernel_idx : kernel_defaults;
+  *a = hint_of(src[0]);
+  *b = hint_of(src[1]);
+  if (s != nullptr) *s = hint_of(src[2]);
+}
+
 // m blocks per scheduling group: as many as keep the group's A blocks (rows x K bf16) within ~24 MB of L2.
 int pick_m_group(int n_mblk, int rows_per_mblk, int k_elems) {
   const int64_t blk_bytes = static_cast<int64_t>(rows_per_mblk) * k_elems * 2;
@@ -791,6 +807,7 @@ int run_fwd(const void* H, const void* W, const void* bias, const int64_t* targe
   sc.n_chunks = n_chunks;
   sc.m_group = pick_m_group(n_mblk, BM * kCG, d);
   sc.n_kblk = ceil_div(d, BK);
+  pick_hints("nnn", 0, &sc.hint_a, &sc.hint_b, nullptr);
   FwdEpi::Params ep;
   ep.targets = targets;
   ep.bias = static_cast<const __nv_bfloat16*>(bias);
@@ -838,6 +855,7 @@ int run_bwd_slab(const void* H, const void* W, const void* bias, const int64_t* 
     sc.m_group = pick_m_group(n_mblk, BM * kCG, d);
     sc.n_kblk = ceil_div(d, BK);
     DzEpi::Params ep;
+    pick_hints("nnn", 1, &sc.hint_a, &sc.hint_b, &ep.store_hint);
     ep.targets = targets;
     ep.bias = static_cast<const __nv_bfloat16*>(bias);
     ep.lse = lse;
@@ -864,6 +882,7 @@ int run_bwd_slab(const void* H, const void* W, const void* bias, const int64_t* 
     sc.n_chunks = sc.n_ntile;
     sc.m_group = 1;  // N tiles of one m block are adjacent: the dZ rows are read from HBM once
     sc.n_kblk = ceil_div(V, BK);
+    pick_hints("nnn", 2, &sc.hint_a, &sc.hint_b, nullptr);
     StoreEpi<false>::Params ep;
     ep.out = dH;
     ep.rows = static_cast<int>(rows);
@@ -886,6 +905,7 @@ int run_bwd_slab(const void* H, const void* W, const void* bias, const int64_t* 
     sc.n_chunks = sc.n_ntile;
     sc.m_group = 1;
     sc.n_kblk = ceil_div(rows, BK);
+    pick_hints("nnn", 3, &sc.hint_a, &sc.hint_b, nullptr);
     if (dw_dtype == FTK_F32) {
       StoreEpi<true>::Params ep;
       ep.out = dW;
