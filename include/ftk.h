@@ -108,7 +108,7 @@ int ftk_lmhead_ce_fwd(const void* H, const void* W, const void* bias, const int6
  * pool at start-up and gives plugins no allocator, and a latency-critical loop
  * that must avoid the device-wide synchronisation cudaMalloc/cudaFree imply.
  * This variant keeps its scratch in a fixed array inside the library's device
- * image (about 4.3 MB per GPU that loads the library, held until exit), so the
+ * image (about 8.5 MB per GPU that loads the library, held until exit), so the
  * call itself performs no allocation of any kind; inputs and outputs are still
  * the caller's buffers.
  *

@@ -31,7 +31,7 @@ constexpr int kAccStages = 2;
 constexpr int kTmemCols = 512;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
-constexpr int kMaxChunks = 32;  // upper bound on vocabulary chunks (sizes the forward workspace)
+constexpr int kMaxChunks = 64;  // upper bound on vocabulary chunks (sizes the forward workspace)
 
 // Work decomposition. A unit is (m block, chunk of consecutive N tiles); units are dealt round-robin to CTAs
 // (or CTA pairs), so the units running at any moment are ~one wave of consecutive unit ids. The ids are ordered so
@@ -1040,7 +1040,8 @@ extern "C" int ftk_lmhead_ce_bwd(const void* H, const void* W, const void* bias,
 // scratch below is part of the library image: a fixed array in device global memory, created when the module is
 // loaded on a GPU and held until the process exits (every GPU that loads the library pays for it once).
 //
-// Limit: M <= FTK_STATIC_MAX_ROWS (16,384 rows, one 8 x 2048 micro-batch); larger calls are rejected.
+// Limit: M <= FTK_STATIC_MAX_ROWS (16,384 rows, one 8 x 2048 micro-batch, 8.5 MB of scratch); larger calls are
+// rejected.
 // The array is shared by every call and keeps whatever the last call left in it.  The only part that must start
 // at zero -- the finalize kernel's arrival counter -- is cleared on the stream at the start of each call; the
 // per-chunk statistics are fully rewritten before they are read.  Two calls whose kernels overlap on the GPU

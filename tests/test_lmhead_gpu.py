@@ -173,3 +173,24 @@ def test_compute_loss_dropin_against_hf_model(cuda_dev):
     got_grad = model.lm_head.weight.grad.detach().float()
     assert abs(float(loss) - float(ref)) <= 3e-3 * abs(float(ref))
     assert O.rel_err(got_grad, ref_grad) < 3e-2  # tied weights: includes the embedding's share, identical on both sides
+
+
+@pytest.mark.parametrize("M,d,V", [(1, 64, 8), (129, 64, 257), (255, 128, 256), (257, 64, 513), (4096, 256, 3000)])
+def test_edge_shapes(cuda_dev, M, d, V):
+    """Single row, sizes one past / one short of the 128-row and 256-column tiles, targets on the last column."""
+    H, W, b, t = mk(M, d, V, seed=M + V, frac_ignore=0.0)
+    t[-1] = V - 1
+    t[0] = 0
+    want = O.lmhead_ce_reference(H, W, None, t)
+    loss, n_valid, lse, dH, dW, _ = gpu_fwd_bwd(H, W, None, t)
+    assert n_valid == M
+    assert abs(loss - float(want["loss"])) <= LOSS_RTOL * abs(float(want["loss"]))
+    assert O.rel_err(dH, want["dH"]) < GRAD_RTOL and O.rel_err(dW, want["dW"]) < GRAD_RTOL
+
+
+def test_results_are_deterministic(cuda_dev):
+    """Fixed-order reductions everywhere on the bias-free path: two runs give the same bits."""
+    H, W, _, t = mk(2048, 256, 5003, seed=9)
+    a = gpu_fwd_bwd(H, W, None, t)
+    b = gpu_fwd_bwd(H, W, None, t)
+    assert a[0] == b[0] and torch.equal(a[2], b[2]) and torch.equal(a[3], b[3]) and torch.equal(a[4], b[4])
