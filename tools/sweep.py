@@ -47,6 +47,10 @@ if __name__ == "__main__":
     run(16 * 1024, 768, 50257, tag="gpt2-124m ctx1024 bs16")
     run(8 * 2048, 2048, 50257, tag="gpt-neo-1.3b ctx2048 bs8")
     run(8 * 2048, 4096, 50400, bias=True, tag="gpt-j-6b ctx2048 bs8")
+    if "--small" in sys.argv:
+        run(2048, 768, 50257, tag="gpt-neo-125m ctx2048 bs1")
+        for d in (768, 1024, 2048, 4096):
+            run(4096, d, 50257, tag="small")
     if "--full" in sys.argv:
         for M in (4096, 16384, 65536, 262144):
             for d in (768, 1024, 2048, 4096):
