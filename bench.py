@@ -202,8 +202,8 @@ def main_gpu(args) -> None:
     L = _lib.lib()
 
     # ---- synthetic inputs, resident in HBM (and a pinned host copy for the e2e leg)
-    from oracle import oracle as O  # only for the seeded token-stream recipe shared with the CPU arm
-    tok_host = torch.from_numpy(O.synth_tokens(N_CTX_FILE, CTX, VOCAB, 7, pad_id=PAD_ID).view(np.int16)).pin_memory()
+    from kubernetes_cloud_b200.tokenfile import synthetic_token_stream
+    tok_host = torch.from_numpy(synthetic_token_stream(N_CTX_FILE, CTX, VOCAB, 7, pad_id=PAD_ID).view(np.int16)).pin_memory()
     tokens = tok_host.to(dev)
     g = torch.Generator(device=dev).manual_seed(42 + rank)
     gw = torch.Generator(device=dev).manual_seed(20240607)  # not the H seed: equal streams make H rows = W rows

@@ -770,7 +770,7 @@ FwdWorkspace carve_fwd(void* base, int64_t M) {
   FwdWorkspace w;
   w.Mpad = round_up(M, 256);
   w.n_blk = static_cast<int>(w.Mpad / 256);
-  uint8_t* p = static_cast<uint8_t*>(base);
+  const uintptr_t p = reinterpret_cast<uintptr_t>(base);  // integer arithmetic: base may be null for a size query
   size_t off = 0;
   w.pmax = reinterpret_cast<float*>(p + off);
   off += sizeof(float) * kMaxChunks * w.Mpad;

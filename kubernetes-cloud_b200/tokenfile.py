@@ -90,3 +90,14 @@ def validate_token_file(path: str, context_length: int, vocab_size: Optional[int
             problems.append(f"pad == eos but non-final contexts {bad} end in padding: their pads would be trained on "
                             "(FT.py:674-687 masks only the final context)")
     return TokenFileReport(path, size, context_length, n_ctx, trailing, max_tok, vocab_ok, padded, convention_ok, problems)
+
+
+def synthetic_token_stream(n_contexts: int, context_length: int, vocab_size: int, seed: int, pad_id: int = 50256,
+                           trailing_pads: int = 300) -> np.ndarray:
+    """The synthetic stream SURVEY.md 8(d) prescribes for benchmarks: uniform uint16 ids from a seeded numpy generator,
+    the final context ending in ``trailing_pads`` pad tokens so the mask rule is exercised."""
+    rng = np.random.default_rng(seed)
+    tok = rng.integers(0, vocab_size, size=n_contexts * context_length, dtype=np.uint16)
+    if trailing_pads:
+        tok[n_contexts * context_length - min(trailing_pads, context_length):] = pad_id
+    return tok
