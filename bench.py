@@ -272,6 +272,78 @@ def main_gpu(args) -> None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t)
 
+    # ================= bulk gather bandwidth (HBM roofline of G1; outside the step: one step's gather is 0.3 MB).
+    # Measured first, on a GPU that is not yet power-capped by the GEMM phase: the kernel tracks the SM/L2 clock. ====
+    n_bulk = 4096 * 8  # 2^26 tokens per launch
+    big_idx = torch.randint(0, N_CTX_FILE, (n_bulk,), device=dev)
+
+    # The kernel is timed through the C ABI into preallocated outputs: going through the torch op would add four
+    # fresh 0.1-0.5 GB allocations per call to the measurement (that path measured 4.3-4.7 TB/s for the same kernel).
+    b_ids = torch.empty(n_bulk, CTX, dtype=torch.int64, device=dev)
+    b_lab = torch.empty_like(b_ids)
+    b_msk = torch.empty(n_bulk, CTX, dtype=torch.bool, device=dev)
+    b_nv = torch.empty(n_bulk, dtype=torch.int32, device=dev)
+
+    def bulk_launch():
+        _lib.check(L.ftk_gather_windows(tokens.data_ptr(), N_CTX_FILE, CTX, big_idx.data_ptr(), n_bulk, PAD_ID, 1, 1,
+                                        b_ids.data_ptr(), b_lab.data_ptr(), b_msk.data_ptr(), b_nv.data_ptr(),
+                                        stream.cuda_stream), "ftk_gather_windows")
+
+    def bulk_gather_gbs() -> float:
+        for _ in range(5):
+            bulk_launch()
+        torch.cuda.synchronize(dev)
+        g0 = torch.cuda.Event(enable_timing=True)
+        g1 = torch.cuda.Event(enable_timing=True)
+        g0.record(stream)
+        for _ in range(10):
+            bulk_launch()
+        g1.record(stream)
+        torch.cuda.synchronize(dev)
+        return 19.0 * n_bulk * CTX / (g0.elapsed_time(g1) / 10 / 1e3) / 1e9
+
+    gather_gbs = bulk_gather_gbs()
+    os.environ["FTK_GATHER_VARIANT"] = "direct"
+    gather_direct_gbs = bulk_gather_gbs()
+    del os.environ["FTK_GATHER_VARIANT"]
+    os.environ["FTK_GATHER_STORES"] = "plain"
+    gather_plain_gbs = bulk_gather_gbs()
+    del os.environ["FTK_GATHER_STORES"]
+    del b_ids, b_lab, b_msk, b_nv
+
+    # ================= optimizer step on the lm_head / wte bucket (HBM roofline) =================
+    n_par = VOCAB * D_MODEL
+    p_bf = W.clone()
+    g_bf = torch.randn(n_par, device=dev, dtype=torch.float32).mul_(1e-3).to(torch.bfloat16)
+    master = p_bf.float().view(-1)
+    m_buf = torch.zeros(n_par, device=dev)
+    v_buf = torch.zeros(n_par, device=dev)
+    sq = torch.zeros(1, device=dev)
+    coef = torch.ones(1, device=dev)
+    ws_n = torch.empty(L.ftk_grad_sqnorm_workspace(), dtype=torch.uint8, device=dev)
+
+    def adam_once(step_no: int):
+        _lib.check(L.ftk_grad_sqnorm(g_bf.data_ptr(), n_par, _lib.FTK_BF16, sq.data_ptr(), 0, ws_n.data_ptr(),
+                                     ws_n.numel(), stream.cuda_stream), "ftk_grad_sqnorm")
+        _lib.check(L.ftk_clip_coef(sq.data_ptr(), 1.0, coef.data_ptr(), stream.cuda_stream), "ftk_clip_coef")
+        _lib.check(L.ftk_adamw_step(p_bf.data_ptr(), g_bf.data_ptr(), master.data_ptr(), m_buf.data_ptr(),
+                                    v_buf.data_ptr(), n_par, _lib.FTK_BF16, _lib.FTK_BF16, 5e-5, 0.9, 0.999, 1e-8, 0.01,
+                                    step_no, 1.0, coef.data_ptr(), stream.cuda_stream), "ftk_adamw_step")
+
+    for i in range(10):
+        adam_once(i + 1)
+    torch.cuda.synchronize(dev)
+    a0 = torch.cuda.Event(enable_timing=True)
+    a1 = torch.cuda.Event(enable_timing=True)
+    a0.record(stream)
+    for i in range(10):
+        adam_once(i + 11)
+    a1.record(stream)
+    torch.cuda.synchronize(dev)
+    adam_ms = a0.elapsed_time(a1) / 10
+    adam_gbs = (28.0 + 2.0) * n_par / (adam_ms / 1e3) / 1e9  # 28 B/param AdamW + 2 B/param gradient-norm read
+    del p_bf, g_bf, master, m_buf, v_buf
+
     nb = len(idx_dev)
     # ================= device-resident leg (value) =================
     sampler = ClockSampler(local)
@@ -351,44 +423,6 @@ def main_gpu(args) -> None:
     h2d = BATCH * CTX * 2 + M * D_MODEL * 2
     d2h = 8
 
-    # ================= bulk gather bandwidth (HBM roofline of G1; outside the step: one step's gather is 0.3 MB) ====
-    n_bulk = 4096 * 8  # 2^26 tokens per launch
-    big_idx = torch.randint(0, N_CTX_FILE, (n_bulk,), device=dev)
-
-    # The kernel is timed through the C ABI into preallocated outputs: going through the torch op would add four
-    # fresh 0.1-0.5 GB allocations per call to the measurement (that path measured 4.3-4.7 TB/s for the same kernel).
-    b_ids = torch.empty(n_bulk, CTX, dtype=torch.int64, device=dev)
-    b_lab = torch.empty_like(b_ids)
-    b_msk = torch.empty(n_bulk, CTX, dtype=torch.bool, device=dev)
-    b_nv = torch.empty(n_bulk, dtype=torch.int32, device=dev)
-
-    def bulk_launch():
-        _lib.check(L.ftk_gather_windows(tokens.data_ptr(), N_CTX_FILE, CTX, big_idx.data_ptr(), n_bulk, PAD_ID, 1, 1,
-                                        b_ids.data_ptr(), b_lab.data_ptr(), b_msk.data_ptr(), b_nv.data_ptr(),
-                                        stream.cuda_stream), "ftk_gather_windows")
-
-    def bulk_gather_gbs() -> float:
-        for _ in range(40):  # ~10 ms: lets the clocks recover from the power-capped GEMM phase before timing
-            bulk_launch()
-        torch.cuda.synchronize(dev)
-        g0 = torch.cuda.Event(enable_timing=True)
-        g1 = torch.cuda.Event(enable_timing=True)
-        g0.record(stream)
-        for _ in range(10):
-            bulk_launch()
-        g1.record(stream)
-        torch.cuda.synchronize(dev)
-        return 19.0 * n_bulk * CTX / (g0.elapsed_time(g1) / 10 / 1e3) / 1e9
-
-    gather_gbs = bulk_gather_gbs()
-    os.environ["FTK_GATHER_VARIANT"] = "direct"
-    gather_direct_gbs = bulk_gather_gbs()
-    del os.environ["FTK_GATHER_VARIANT"]
-    os.environ["FTK_GATHER_STORES"] = "plain"
-    gather_plain_gbs = bulk_gather_gbs()
-    del os.environ["FTK_GATHER_STORES"]
-    del b_ids, b_lab, b_msk, b_nv
-
     if handle is not None:
         L.ftk_dp_destroy(handle)
     if rank != 0:
@@ -433,6 +467,10 @@ def main_gpu(args) -> None:
                             "frac": gather_gbs / peaks["hbm"],
                             "note": "bulk launch of 2^26 tokens, 19 B/token, streaming stores, timed through the C ABI",
                             "direct_variant_gbs": gather_direct_gbs, "plain_stores_gbs": gather_plain_gbs,},
+        "roofline_adamw": {"bound": "hbm", "achieved": adam_gbs, "peak": peaks["hbm"], "unit": "GB/s",
+                           "frac": adam_gbs / peaks["hbm"], "ms": adam_ms,
+                           "note": "grad-norm + clip + fused AdamW on the 103M-element bf16 lm_head bucket, 30 B/param; "
+                                   "not part of the timed step"},
         "e2e": {"value": e2e_value, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms / args.steps,
                 "note": "token windows + hidden states from pinned host memory each step, loss and count read back"},

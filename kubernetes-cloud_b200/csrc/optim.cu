@@ -146,11 +146,13 @@ __global__ void __launch_bounds__(kThreads) adamw_bf16_kernel(__nv_bfloat16* __r
   const size_t n8 = n / 8;
   for (size_t i = blockIdx.x * static_cast<size_t>(kThreads) + threadIdx.x; i < n8;
        i += static_cast<size_t>(gridDim.x) * kThreads) {
-    const uint4 gv = reinterpret_cast<const uint4*>(g)[i];
+    // optimizer state is touched once per step: streaming loads and stores keep it from displacing anything in L2
+    const uint4 gv = __ldcs(reinterpret_cast<const uint4*>(g) + i);
     const uint32_t gw[4] = {gv.x, gv.y, gv.z, gv.w};
-    float4 w0 = reinterpret_cast<float4*>(master)[2 * i], w1 = reinterpret_cast<float4*>(master)[2 * i + 1];
-    float4 m0 = reinterpret_cast<float4*>(m)[2 * i], m1 = reinterpret_cast<float4*>(m)[2 * i + 1];
-    float4 v0 = reinterpret_cast<float4*>(v)[2 * i], v1 = reinterpret_cast<float4*>(v)[2 * i + 1];
+    float4 w0 = __ldcs(reinterpret_cast<const float4*>(master) + 2 * i);
+    float4 w1 = __ldcs(reinterpret_cast<const float4*>(master) + 2 * i + 1);
+    float4 m0 = __ldcs(reinterpret_cast<const float4*>(m) + 2 * i), m1 = __ldcs(reinterpret_cast<const float4*>(m) + 2 * i + 1);
+    float4 v0 = __ldcs(reinterpret_cast<const float4*>(v) + 2 * i), v1 = __ldcs(reinterpret_cast<const float4*>(v) + 2 * i + 1);
     float gg[8];
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
@@ -166,12 +168,12 @@ __global__ void __launch_bounds__(kThreads) adamw_bf16_kernel(__nv_bfloat16* __r
     w1.y = adamw_one(w1.y, gg[5], m1.y, v1.y, a, gs);
     w1.z = adamw_one(w1.z, gg[6], m1.z, v1.z, a, gs);
     w1.w = adamw_one(w1.w, gg[7], m1.w, v1.w, a, gs);
-    reinterpret_cast<float4*>(master)[2 * i] = w0;
-    reinterpret_cast<float4*>(master)[2 * i + 1] = w1;
-    reinterpret_cast<float4*>(m)[2 * i] = m0;
-    reinterpret_cast<float4*>(m)[2 * i + 1] = m1;
-    reinterpret_cast<float4*>(v)[2 * i] = v0;
-    reinterpret_cast<float4*>(v)[2 * i + 1] = v1;
+    __stcs(reinterpret_cast<float4*>(master) + 2 * i, w0);
+    __stcs(reinterpret_cast<float4*>(master) + 2 * i + 1, w1);
+    __stcs(reinterpret_cast<float4*>(m) + 2 * i, m0);
+    __stcs(reinterpret_cast<float4*>(m) + 2 * i + 1, m1);
+    __stcs(reinterpret_cast<float4*>(v) + 2 * i, v0);
+    __stcs(reinterpret_cast<float4*>(v) + 2 * i + 1, v1);
     uint4 o;
     __nv_bfloat162 h;
     h = __floats2bfloat162_rn(w0.x, w0.y);
