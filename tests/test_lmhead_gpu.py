@@ -194,3 +194,41 @@ def test_results_are_deterministic(cuda_dev):
     a = gpu_fwd_bwd(H, W, None, t)
     b = gpu_fwd_bwd(H, W, None, t)
     assert a[0] == b[0] and torch.equal(a[2], b[2]) and torch.equal(a[3], b[3]) and torch.equal(a[4], b[4])
+
+
+def test_hot_path_replays_from_a_cuda_graph(cuda_dev):
+    """gather -> forward -> backward captured once into a CUDA graph and replayed on new data: the C ABI only issues
+    stream-ordered work (memset, kernels) on the stream it is given, and tensor maps travel as kernel parameters."""
+    from kubernetes_cloud_b200 import ops  # noqa: F401
+    T, n_ctx, B, d, V = 256, 16, 4, 128, 3000
+    tok = torch.from_numpy(O.synth_tokens(n_ctx, T, V, 3, pad_id=V - 1, trailing_pads=20).view(np.int16)).cuda()
+    idx = torch.tensor([3, 15, 0, 7], device="cuda")
+    H, W, _, _ = mk(B * T, d, V, seed=21)
+    Hs, Ws = H.cuda(), W.cuda()
+
+    def step():
+        ids, targets, mask, _ = torch.ops.ftk.gather_windows(tok, idx, T, V - 1, True, True)
+        ls, nv, lse = torch.ops.ftk.lmhead_ce_fwd(Hs, Ws, None, targets.view(-1))
+        dH, dW, _ = torch.ops.ftk.lmhead_ce_bwd(Hs, Ws, None, targets.view(-1), lse, None, nv, 1.0, False)
+        return ls, nv, dH, dW
+
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):  # warm-up outside capture: function attributes, lazy module loading
+        for _ in range(2):
+            step()
+    torch.cuda.current_stream().wait_stream(side)
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(graph):
+        out = step()
+    # new inputs in the same buffers, then replay
+    H2, _, _, _ = mk(B * T, d, V, seed=22)
+    Hs.copy_(H2.cuda())
+    idx.copy_(torch.tensor([1, 2, 15, 9], device="cuda"))
+    graph.replay()
+    torch.cuda.synchronize()
+    got = [o.clone() for o in out]
+    want = step()
+    torch.cuda.synchronize()
+    assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1])
+    assert torch.equal(got[2], want[2]) and torch.equal(got[3], want[3])
