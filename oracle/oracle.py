@@ -222,3 +222,14 @@ def adamw_reference(params, grads_per_step, lrs, betas=(0.9, 0.999), eps=1e-8, w
             norms.append(float(torch.nn.utils.clip_grad_norm_(ps, max_grad_norm)))
         opt.step()
     return [p.detach() for p in ps], norms
+
+
+def hf_causal_lm_loss_v428(logits: torch.Tensor, labels: torch.Tensor) -> torch.Tensor:
+    """The formulation of the transformers release the reference pins (~=4.28.1, e.g. GPTNeoForCausalLM.forward):
+    ``shift_logits = logits[..., :-1, :]``, ``shift_labels = labels[..., 1:]``, ``CrossEntropyLoss()`` on the
+    flattened pair after an fp32 upcast.  Restated from the published source of that version, which is not installed
+    here; arithmetically the same mean as ``hf_causal_lm_loss`` (5.x pads the labels instead of slicing the logits)."""
+    logits = logits.to(torch.float32)
+    shift_logits = logits[..., :-1, :].contiguous()
+    shift_labels = labels[..., 1:].contiguous()
+    return torch.nn.CrossEntropyLoss()(shift_logits.view(-1, shift_logits.size(-1)), shift_labels.view(-1))
