@@ -32,7 +32,7 @@ class _Bucket:
 
 
 class GradSync:
-    def __init__(self, params: Iterable[torch.nn.Parameter], rank: int, world: int, bucket_bytes: int = 64 << 20,
+    def __init__(self, params: Iterable[torch.nn.Parameter], rank: int, world: int, bucket_bytes: int = 128 << 20,
                  backend: str = "ftk", grad_dtype: Optional[torch.dtype] = None, average: bool = True):
         self.rank, self.world, self.backend, self.average = rank, world, backend, average
         self.params = [p for p in params if p.requires_grad]
