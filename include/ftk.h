@@ -99,6 +99,29 @@ int ftk_lmhead_ce_fwd(const void* H, const void* W, const void* bias, const int6
                       size_t workspace_bytes, void* stream);
 
 /*
+ * Opt-in pair that trades memory for speed. ftk_lmhead_ce_fwd_keep is the forward above, and
+ * additionally leaves the softmax numerators exp(z - c) in bf16 in `probs` ([M][round_up(V,64)],
+ * ftk_lmhead_ce_probs_bytes) with the per-(256-column tile, row) reference maxima c in `cref`
+ * (ftk_lmhead_ce_cref_bytes); c is the row's running maximum, so the exponent is never positive.
+ * ftk_lmhead_ce_bwd_kept turns `probs` into dZ in place (one HBM-bound elementwise pass:
+ * dZ = probs * exp(c - lse) * scale - onehot * scale) and runs the dH and dW GEMMs: the logit
+ * recompute GEMM of ftk_lmhead_ce_bwd (a quarter of the tensor work of a training step) is gone.
+ * Cost: the [M][V] bf16 array now lives from forward to backward instead of only inside the
+ * backward, which is why this is not the default. `probs` is consumed by the backward.
+ * Same results as the recompute path up to one extra bf16 rounding of the numerators.
+ * No counterpart in the reference beyond the autograd it replaces (see ftk_lmhead_ce_bwd).
+ */
+size_t ftk_lmhead_ce_probs_bytes(int64_t M, int32_t V);
+size_t ftk_lmhead_ce_cref_bytes(int64_t M, int32_t V);
+int ftk_lmhead_ce_fwd_keep(const void* H, const void* W, const void* bias, const int64_t* targets, int64_t M, int32_t d,
+                           int32_t V, float* lse, float* loss_sum, int32_t* n_valid, void* probs, float* cref,
+                           void* workspace, size_t workspace_bytes, void* stream);
+int ftk_lmhead_ce_bwd_kept(const void* H, const void* W, const int64_t* targets, const float* lse, void* probs,
+                           const float* cref, int64_t M, int32_t d, int32_t V, float grad_scale,
+                           const float* grad_scale_dev, const int32_t* n_valid_dev, void* dH, void* dW, int32_t dw_dtype,
+                           int32_t accumulate, float* dbias, void* stream);
+
+/*
  * The same forward for callers that cannot allocate device memory. It has no
  * counterpart in the reference.
  *

@@ -25,6 +25,13 @@ SIGNATURES = {
     "ftk_lmhead_ce_fwd_workspace": (c_size_t, [c_int64, c_int32, c_int32]),
     "ftk_lmhead_ce_fwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p,
                                     c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "ftk_lmhead_ce_probs_bytes": (c_size_t, [c_int64, c_int32]),
+    "ftk_lmhead_ce_cref_bytes": (c_size_t, [c_int64, c_int32]),
+    "ftk_lmhead_ce_fwd_keep": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p,
+                                         c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "ftk_lmhead_ce_bwd_kept": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32,
+                                         c_int32, c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int32,
+                                         c_void_p, c_void_p]),
     "ftk_lmhead_ce_fwd_static": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p,
                                            c_void_p, c_void_p, c_void_p]),
     "ftk_lmhead_ce_bwd_workspace": (c_size_t, [c_int64, c_int32, c_int32, c_int64]),

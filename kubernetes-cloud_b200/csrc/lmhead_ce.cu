@@ -246,6 +246,135 @@ struct DzEpi {
   }
 };
 
+// Forward that also keeps the softmax numerators (opt-in; see ftk_lmhead_ce_fwd_keep): same statistics as FwdEpi,
+// and every tile additionally leaves exp(z - c) in bf16 in a [rows][ld] slab, c = the row's running maximum after
+// that tile (written to cref[tile][row]).  c is a true maximum, so the exponent is <= 0 and nothing can overflow.
+// The backward then needs no logit recompute: dZ = numerators * exp(c - lse) * scale - onehot * scale, elementwise.
+struct FwdKeepEpi {
+  static constexpr uint32_t kSmemBytes = 4 * 2 * 4096;  // staging for the TMA stores, as in DzEpi
+  struct Params {
+    CUtensorMap tm_out;         // numerators slab, bf16 [rows][ld], box 64 columns x 32 rows, 128-byte swizzle
+    const int64_t* targets;     // [M]
+    const __nv_bfloat16* bias;  // [V] or null
+    float* pmax;                // [n_chunks][Mpad]
+    float* psum;                // [n_chunks][Mpad]
+    float* ztgt;                // [Mpad]
+    float* cref;                // [n_ntile][Mpad] reference maximum of each (tile, row)
+    uint64_t store_hint;
+    int M, V, Mpad, ld;
+  };
+  struct State {
+    float m, s, zt;
+    int tgt, row, chunk;
+    bool has;
+    uint32_t nstore;  // survives across units: parity of the staging buffers
+  };
+  template <int BN>
+  static __device__ __forceinline__ void begin_unit(State& st, const Params& p, int row, int chunk) {
+    st.row = row;
+    st.chunk = chunk;
+    st.m = -INFINITY;
+    st.s = 0.f;
+    st.zt = 0.f;
+    st.has = false;
+    st.tgt = (row < p.M) ? static_cast<int>(p.targets[row]) : -1;
+  }
+  template <int BN>
+  static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0, const EpiCtx& cx) {
+    // ---- pass 1 over the accumulator: row maximum of this tile (and the target logit)
+    float tmax = -INFINITY;
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      const int col0 = n0 + c * 32;
+      if (col0 >= p.V) break;  // warp-uniform
+      float v[32];
+      tmem_ld32(taddr + c * 32, v);
+      tmem_ld_wait();
+      if (p.bias != nullptr) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j < p.V) v[j] += __bfloat162float(__ldg(p.bias + col0 + j));
+      }
+      if (col0 + 32 > p.V) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (col0 + j >= p.V) v[j] = -INFINITY;
+      }
+      if (st.tgt >= col0 && st.tgt < col0 + 32) {
+        const int jj = st.tgt - col0;
+#pragma unroll
+        for (int j = 0; j < 32; ++j)
+          if (j == jj) st.zt = v[j];
+        st.has = true;
+      }
+#pragma unroll
+      for (int j = 0; j < 32; ++j) tmax = fmaxf(tmax, v[j]);
+    }
+    const float m_new = fmaxf(st.m, tmax);  // finite: column n0 < V is real
+    const float neg = -m_new * kLog2e;
+    st.s *= exp2f(fmaf(st.m, kLog2e, neg));  // exp2(-inf) = 0 on the first tile of a unit
+    st.m = m_new;
+    if (st.row < p.M) p.cref[static_cast<size_t>(n0 / BN) * p.Mpad + st.row] = m_new;
+    // ---- pass 2: numerators relative to m_new, summed in fp32 and stored in bf16
+    uint8_t* warp_buf = cx.smem + cx.q * 8192;
+    const int row0 = st.row - cx.lane;
+    float acc = 0.f;
+#pragma unroll 1
+    for (int g = 0; g < BN / 64; ++g) {
+      const int col0 = n0 + g * 64;
+      if (col0 >= p.ld) break;  // warp-uniform
+      uint8_t* buf = warp_buf + (st.nstore & 1) * 4096;
+      if (cx.lane == 0) tma_store_wait_read<1>();
+      __syncwarp();
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        const int c0 = col0 + h * 32;
+        float v[32];
+        tmem_ld32(taddr + g * 64 + h * 32, v);
+        tmem_ld_wait();
+        if (p.bias != nullptr) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (c0 + j < p.V) v[j] += __bfloat162float(__ldg(p.bias + c0 + j));
+        }
+        uint32_t w[16];
+#pragma unroll
+        for (int j = 0; j < 32; j += 2) {
+          const float e0 = (c0 + j < p.V) ? exp2f(fmaf(v[j], kLog2e, neg)) : 0.f;
+          const float e1 = (c0 + j + 1 < p.V) ? exp2f(fmaf(v[j + 1], kLog2e, neg)) : 0.f;
+          acc += e0 + e1;
+          w[j >> 1] = pack_bf16x2(e0, e1);
+        }
+#pragma unroll
+        for (int qq = 0; qq < 4; ++qq) {
+          const int c = h * 4 + qq;
+          uint4* dst = reinterpret_cast<uint4*>(buf + cx.lane * 128 + ((c ^ (cx.lane & 7)) << 4));
+          *dst = make_uint4(w[4 * qq], w[4 * qq + 1], w[4 * qq + 2], w[4 * qq + 3]);
+        }
+      }
+      fence_async_shared();
+      __syncwarp();
+      if (cx.lane == 0) {
+        tma_store_2d_hint(&p.tm_out, buf, col0, row0, p.store_hint);
+        tma_store_commit();
+      }
+      ++st.nstore;
+    }
+    st.s += acc;
+  }
+  template <int BN>
+  static __device__ __forceinline__ void end_unit(State& st, const Params& p) {
+    if (st.row < p.M) {
+      p.pmax[static_cast<size_t>(st.chunk) * p.Mpad + st.row] = st.m;
+      p.psum[static_cast<size_t>(st.chunk) * p.Mpad + st.row] = st.s;
+      if (st.has) p.ztgt[st.row] = st.zt;
+    }
+  }
+  static __device__ __forceinline__ void finish(const EpiCtx& cx) {
+    if (cx.lane == 0) tma_store_wait_all<0>();
+  }
+};
+
 // Plain GEMM epilogue: out[row, col] (+)= acc, bf16 or fp32 row-major.
 template <bool kF32>
 struct StoreEpi {
@@ -621,6 +750,40 @@ __global__ void __launch_bounds__(128) dbias_kernel(const __nv_bfloat16* __restr
   if (col + 1 < V) atomicAdd(dbias + col + 1, a1);
 }
 
+
+// Kept numerators -> dZ in place: dZ[r, c] = e[r, c] * exp(cref[tile(c)][r] - lse[r]) * scale_r - (c == target_r) * scale_r,
+// scale_r = 0 on ignored rows.  HBM-bound: one 16-byte load and store per thread.
+__global__ void __launch_bounds__(256) probs_to_dz_kernel(__nv_bfloat16* __restrict__ probs,
+                                                          const float* __restrict__ cref,
+                                                          const float* __restrict__ lse,
+                                                          const int64_t* __restrict__ targets, int rows, int V, int ld,
+                                                          int Mpad, int tile_cols, float scale,
+                                                          const float* __restrict__ scale_dev,
+                                                          const int32_t* __restrict__ nvalid_dev) {
+  const int r = blockIdx.y;
+  const int c8 = (blockIdx.x * 256 + threadIdx.x) * 8;
+  if (r >= rows || c8 >= ld) return;
+  const int tgt = static_cast<int>(targets[r]);
+  float sc = scale;
+  if (scale_dev != nullptr) sc *= __ldg(scale_dev);
+  if (nvalid_dev != nullptr) sc /= static_cast<float>(__ldg(nvalid_dev));
+  if (tgt < 0) sc = 0.f;
+  const float f = exp2f((__ldg(cref + static_cast<size_t>(c8 / tile_cols) * Mpad + r) - __ldg(lse + r)) * kLog2e) * sc;
+  uint4* ptr = reinterpret_cast<uint4*>(probs + static_cast<size_t>(r) * ld + c8);
+  const uint4 in = __ldcs(ptr);
+  const uint32_t iw[4] = {in.x, in.y, in.z, in.w};
+  uint32_t ow[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&iw[e]);
+    float a = __low2float(h) * f, b = __high2float(h) * f;
+    if (c8 + 2 * e == tgt) a -= sc;
+    if (c8 + 2 * e + 1 == tgt) b -= sc;
+    ow[e] = pack_bf16x2(a, b);
+  }
+  *ptr = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+}
+
 // ------------------------------------------------------------------------------------------------ host side
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -826,8 +989,56 @@ int run_fwd(const void* H, const void* W, const void* bias, const int64_t* targe
   return FTK_OK;
 }
 
+// Forward that keeps the softmax numerators (FwdKeepEpi) for a recompute-free backward.
+template <int kCG>
+int run_fwd_keep(const void* H, const void* W, const void* bias, const int64_t* targets, int64_t M, int d, int V,
+                 float* lse, float* loss_sum, int32_t* n_valid, __nv_bfloat16* probs, float* cref,
+                 const FwdWorkspace& ws, int sm_count, cudaStream_t st) {
+  constexpr int BN = 256;
+  constexpr int kStages = (kCG == 1) ? 4 : 6;
+  const int64_t ld = round_up(V, 64);
+  CUtensorMap tmA, tmB;
+  if (int rc = make_tmap(&tmA, H, d, M, static_cast<uint64_t>(d) * 2, BK, BM)) return rc;
+  if (int rc = make_tmap(&tmB, W, d, V, static_cast<uint64_t>(d) * 2, BK, BN / kCG)) return rc;
+  Sched sc;
+  const int n_mblk = ceil_div(M, BM * kCG);
+  sc.n_ntile = ceil_div(V, BN);
+  int n_chunks;
+  plan_chunks(n_mblk, sc.n_ntile, (sm_count - g_sm_reserve > kCG ? sm_count - g_sm_reserve : kCG) / kCG, &n_chunks,
+              &sc.tiles_per_chunk);
+  sc.n_units = n_mblk * n_chunks;
+  sc.n_mblk = n_mblk;
+  sc.n_chunks = n_chunks;
+  sc.m_group = pick_m_group(n_mblk, BM * kCG, d);
+  sc.n_kblk = ceil_div(d, BK);
+  FwdKeepEpi::Params ep;
+  pick_hints("nnn", 0, &sc.hint_a, &sc.hint_b, &ep.store_hint);
+  if (int rc = make_tmap(&ep.tm_out, probs, ld, M, static_cast<uint64_t>(ld) * 2, 64, 32)) return rc;
+  ep.targets = targets;
+  ep.bias = static_cast<const __nv_bfloat16*>(bias);
+  ep.pmax = ws.pmax;
+  ep.psum = ws.psum;
+  ep.ztgt = ws.ztgt;
+  ep.cref = cref;
+  ep.M = static_cast<int>(M);
+  ep.V = V;
+  ep.Mpad = static_cast<int>(ws.Mpad);
+  ep.ld = static_cast<int>(ld);
+  FTK_CUDA_CHECK(cudaMemsetAsync(ws.ticket, 0, sizeof(unsigned int), st));
+  if (int rc = launch_umma<kCG, BN, kStages, false, false, FwdKeepEpi>(tmA, tmB, sc, ep, sm_count, st)) return rc;
+  fwd_finalize_kernel<<<ceil_div(M, 256), 256, 0, st>>>(ws.pmax, ws.psum, ws.ztgt, targets, static_cast<int>(M),
+                                                        static_cast<int>(ws.Mpad), n_chunks, lse, ws.blk_loss,
+                                                        ws.blk_cnt, ws.ticket, loss_sum, n_valid);
+  FTK_CUDA_CHECK(cudaGetLastError());
+  return FTK_OK;
+}
+
 constexpr int64_t kDefaultSlabRows = 16384;
 inline int64_t dz_pitch(int V) { return round_up(V, 64); }  // bf16 elements; rows start 128-byte aligned
+
+template <int kCG>
+int run_grad_gemms(const void* H, const void* W, int64_t rows, int d, int V, void* dH, void* dW, int dw_dtype,
+                   int accumulate, float* dbias, __nv_bfloat16* dz, int sm_count, cudaStream_t st);
 
 template <int kCG>
 int run_bwd_slab(const void* H, const void* W, const void* bias, const int64_t* targets, const float* lse,
@@ -868,6 +1079,15 @@ int run_bwd_slab(const void* H, const void* W, const void* bias, const int64_t* 
     ep.ld = static_cast<int>(ld);
     if (int rc = launch_umma<kCG, BN, kStages, false, false, DzEpi>(tmA, tmB, sc, ep, sm_count, st)) return rc;
   }
+  return run_grad_gemms<kCG>(H, W, rows, d, V, dH, dW, dw_dtype, accumulate, dbias, dz, sm_count, st);
+}
+
+template <int kCG>
+int run_grad_gemms(const void* H, const void* W, int64_t rows, int d, int V, void* dH, void* dW, int dw_dtype,
+                   int accumulate, float* dbias, __nv_bfloat16* dz, int sm_count, cudaStream_t st) {
+  constexpr int BN = 256;
+  constexpr int kStages = (kCG == 1) ? 4 : 6;
+  const int64_t ld = dz_pitch(V);
   // ---- stage 2: dH[rows, d] = dZ[rows, V] . W[V, d]
   {
     CUtensorMap tmA, tmB;
@@ -1028,6 +1248,75 @@ extern "C" int ftk_lmhead_ce_bwd(const void* H, const void* W, const void* bias,
     if (rc) return rc;
   }
   return FTK_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Opt-in pair: the forward keeps the softmax numerators, the backward skips the logit recompute.
+extern "C" size_t ftk_lmhead_ce_probs_bytes(int64_t M, int32_t V) {
+  if (M <= 0 || V <= 0) return 0;
+  return static_cast<size_t>(M) * static_cast<size_t>(round_up(V, 64)) * 2;
+}
+
+extern "C" size_t ftk_lmhead_ce_cref_bytes(int64_t M, int32_t V) {
+  if (M <= 0 || V <= 0) return 0;
+  return static_cast<size_t>(ceil_div(V, 256)) * static_cast<size_t>(round_up(M, 256)) * sizeof(float);
+}
+
+extern "C" int ftk_lmhead_ce_fwd_keep(const void* H, const void* W, const void* bias, const int64_t* targets,
+                                      int64_t M, int32_t d, int32_t V, float* lse, float* loss_sum, int32_t* n_valid,
+                                      void* probs, float* cref, void* workspace, size_t workspace_bytes,
+                                      void* stream) {
+  ftk::DeviceInfo di;
+  if (int rc = check_common(H, W, M, d, V, &di)) return rc;
+  FTK_REQUIRE(targets && lse && loss_sum && n_valid && probs && cref && workspace,
+              "ftk_lmhead_ce_fwd_keep: null pointer argument");
+  FTK_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0 && (reinterpret_cast<uintptr_t>(probs) & 127) == 0,
+              "ftk_lmhead_ce_fwd_keep: workspace must be 256-byte and probs 128-byte aligned");
+  const FwdWorkspace ws = carve_fwd(workspace, M);
+  if (workspace_bytes < ws.bytes)
+    return ftk::fail(FTK_EWORKSPACE, "ftk_lmhead_ce_fwd_keep: workspace %zu bytes < required %zu", workspace_bytes,
+                     ws.bytes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (cta_group() == 2 && di.sm_count >= 2)
+    return run_fwd_keep<2>(H, W, bias, targets, M, d, V, lse, loss_sum, n_valid, static_cast<__nv_bfloat16*>(probs),
+                           cref, ws, di.sm_count, st);
+  return run_fwd_keep<1>(H, W, bias, targets, M, d, V, lse, loss_sum, n_valid, static_cast<__nv_bfloat16*>(probs), cref,
+                         ws, di.sm_count, st);
+}
+
+extern "C" int ftk_lmhead_ce_bwd_kept(const void* H, const void* W, const int64_t* targets, const float* lse,
+                                      void* probs, const float* cref, int64_t M, int32_t d, int32_t V,
+                                      float grad_scale, const float* grad_scale_dev, const int32_t* n_valid_dev,
+                                      void* dH, void* dW, int32_t dw_dtype, int32_t accumulate, float* dbias,
+                                      void* stream) {
+  ftk::DeviceInfo di;
+  if (int rc = check_common(H, W, M, d, V, &di)) return rc;
+  FTK_REQUIRE(targets && lse && probs && cref && dH && dW, "ftk_lmhead_ce_bwd_kept: null pointer argument");
+  FTK_REQUIRE(dw_dtype == FTK_BF16 || dw_dtype == FTK_F32, "ftk_lmhead_ce_bwd_kept: bad dw_dtype %d", dw_dtype);
+  FTK_REQUIRE((reinterpret_cast<uintptr_t>(dH) & 15) == 0 && (reinterpret_cast<uintptr_t>(dW) & 15) == 0,
+              "ftk_lmhead_ce_bwd_kept: dH/dW must be 16-byte aligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int64_t ld = dz_pitch(V);
+  if (dbias != nullptr && !accumulate) FTK_CUDA_CHECK(cudaMemsetAsync(dbias, 0, sizeof(float) * V, st));
+  {
+    dim3 grid(ceil_div(ld, 256 * 8), static_cast<unsigned>(M));
+    FTK_REQUIRE(M <= 65535 * 64, "ftk_lmhead_ce_bwd_kept: M too large");
+    // gridDim.y is limited to 65535: fold rows beyond that into several launches
+    for (int64_t r0 = 0; r0 < M; r0 += 65535) {
+      const int rows = static_cast<int>(M - r0 < 65535 ? M - r0 : 65535);
+      grid.y = rows;
+      probs_to_dz_kernel<<<grid, 256, 0, st>>>(static_cast<__nv_bfloat16*>(probs) + static_cast<size_t>(r0) * ld,
+                                               cref + r0, lse + r0, targets + r0, rows, V, static_cast<int>(ld),
+                                               static_cast<int>(round_up(M, 256)), 256, grad_scale, grad_scale_dev,
+                                               n_valid_dev);
+    }
+    FTK_CUDA_CHECK(cudaGetLastError());
+  }
+  if (cta_group() == 2 && di.sm_count >= 2)
+    return run_grad_gemms<2>(H, W, M, d, V, dH, dW, dw_dtype, accumulate, dbias, static_cast<__nv_bfloat16*>(probs),
+                             di.sm_count, st);
+  return run_grad_gemms<1>(H, W, M, d, V, dH, dW, dw_dtype, accumulate, dbias, static_cast<__nv_bfloat16*>(probs),
+                           di.sm_count, st);
 }
 
 // ------------------------------------------------------------------------------------------------

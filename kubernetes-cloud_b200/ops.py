@@ -163,24 +163,128 @@ def _(H, W, bias, targets, lse, grad_out, n_valid, grad_scale, dw_fp32):
             H.new_empty((W.shape[0] if bias is not None else 0,), dtype=torch.float32))
 
 
+@torch.library.custom_op("ftk::lmhead_ce_fwd_keep", mutates_args=())
+def lmhead_ce_fwd_keep(H: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor], targets: torch.Tensor
+                       ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
+    """The forward that also keeps the softmax numerators: returns (loss_sum, n_valid, lse, probs bf16 [M, ld],
+    cref fp32 [n_tiles, Mpad]) for ``lmhead_ce_bwd_kept``."""
+    global _launches
+    _check_hw(H, W, bias, targets)
+    M, d = H.shape
+    V = W.shape[0]
+    dev = H.device
+    L = _lib.lib()
+    lse = torch.empty((M,), dtype=torch.float32, device=dev)
+    loss_sum = torch.empty((1,), dtype=torch.float32, device=dev)
+    n_valid = torch.empty((1,), dtype=torch.int32, device=dev)
+    ld = (V + 63) // 64 * 64
+    probs = torch.empty((M, ld), dtype=torch.bfloat16, device=dev)
+    cref = torch.empty((L.ftk_lmhead_ce_cref_bytes(M, V) // 4,), dtype=torch.float32, device=dev)
+    ws_bytes = L.ftk_lmhead_ce_fwd_workspace(M, d, V)
+    ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        rc = L.ftk_lmhead_ce_fwd_keep(H.data_ptr(), W.data_ptr(), _ptr(bias), targets.data_ptr(), M, d, V,
+                                      lse.data_ptr(), loss_sum.data_ptr(), n_valid.data_ptr(), probs.data_ptr(),
+                                      cref.data_ptr(), ws.data_ptr(), ws_bytes, _stream(H))
+    _lib.check(rc, "ftk_lmhead_ce_fwd_keep")
+    _launches += 2
+    return loss_sum, n_valid, lse, probs, cref
+
+
+@lmhead_ce_fwd_keep.register_fake
+def _(H, W, bias, targets):
+    M, V = H.shape[0], W.shape[0]
+    return (H.new_empty((1,), dtype=torch.float32), H.new_empty((1,), dtype=torch.int32),
+            H.new_empty((M,), dtype=torch.float32), H.new_empty((M, (V + 63) // 64 * 64)),
+            H.new_empty(((V + 255) // 256 * ((M + 255) // 256 * 256),), dtype=torch.float32))
+
+
+@torch.library.custom_op("ftk::lmhead_ce_bwd_kept", mutates_args=("probs",))
+def lmhead_ce_bwd_kept(H: torch.Tensor, W: torch.Tensor, has_bias: bool, targets: torch.Tensor, lse: torch.Tensor,
+                       probs: torch.Tensor, cref: torch.Tensor, grad_out: Optional[torch.Tensor],
+                       n_valid: Optional[torch.Tensor], grad_scale: float, dw_fp32: bool
+                       ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """Backward from kept numerators (no logit recompute).  ``probs`` is overwritten with dZ."""
+    global _launches
+    _check_hw(H, W, None, targets)
+    _need_cuda(lse, probs, cref, grad_out, n_valid)
+    M, d = H.shape
+    V = W.shape[0]
+    dev = H.device
+    dH = torch.empty((M, d), dtype=torch.bfloat16, device=dev)
+    dW = torch.empty((V, d), dtype=torch.float32 if dw_fp32 else torch.bfloat16, device=dev)
+    dbias = torch.empty((V if has_bias else 0,), dtype=torch.float32, device=dev)
+    if grad_out is not None:
+        grad_out = grad_out.to(torch.float32).contiguous()
+    with torch.cuda.device(dev):
+        rc = _lib.lib().ftk_lmhead_ce_bwd_kept(H.data_ptr(), W.data_ptr(), targets.data_ptr(), lse.data_ptr(),
+                                               probs.data_ptr(), cref.data_ptr(), M, d, V, grad_scale, _ptr(grad_out),
+                                               _ptr(n_valid), dH.data_ptr(), dW.data_ptr(),
+                                               _lib.FTK_F32 if dw_fp32 else _lib.FTK_BF16, 0,
+                                               dbias.data_ptr() if has_bias else 0, _stream(H))
+    _lib.check(rc, "ftk_lmhead_ce_bwd_kept")
+    _launches += 3 + (1 if has_bias else 0) + (M + 65534) // 65535 - 1
+    return dH, dW, dbias
+
+
+@lmhead_ce_bwd_kept.register_fake
+def _(H, W, has_bias, targets, lse, probs, cref, grad_out, n_valid, grad_scale, dw_fp32):
+    return (torch.empty_like(H), W.new_empty(W.shape, dtype=torch.float32 if dw_fp32 else torch.bfloat16),
+            H.new_empty((W.shape[0] if has_bias else 0,), dtype=torch.float32))
+
+
+_backward_mode = "recompute"
+_keep_budget_bytes = 8 << 30
+
+
+def set_backward_mode(mode: str, keep_budget_bytes: int = 8 << 30) -> None:
+    """"recompute" (default): nothing of size [tokens, vocab] survives the forward; the backward recomputes the
+    logits tile by tile.  "keep": the forward also stores the bf16 softmax numerators (tokens x vocab x 2 bytes, used
+    only while they fit ``keep_budget_bytes``), and the backward skips the recompute GEMM -- about a quarter less
+    tensor work per training step."""
+    global _backward_mode, _keep_budget_bytes
+    if mode not in ("recompute", "keep"):
+        raise ValueError(mode)
+    _backward_mode, _keep_budget_bytes = mode, int(keep_budget_bytes)
+
+
 class _FusedLmHeadCE(torch.autograd.Function):
     @staticmethod
     def forward(ctx, hidden, weight, bias, targets):
-        loss_sum, n_valid, lse = torch.ops.ftk.lmhead_ce_fwd(hidden, weight, bias, targets)
-        ctx.save_for_backward(hidden, weight, bias, targets, lse, n_valid)
+        M, V = hidden.shape[0], weight.shape[0]
+        keep = (_backward_mode == "keep" and torch.is_grad_enabled()
+                and _lib.lib().ftk_lmhead_ce_probs_bytes(M, V) <= _keep_budget_bytes)
+        ctx.keep = keep
+        if keep:
+            loss_sum, n_valid, lse, probs, cref = torch.ops.ftk.lmhead_ce_fwd_keep(hidden, weight, bias, targets)
+            ctx.save_for_backward(hidden, weight, bias, targets, lse, n_valid, probs, cref)
+        else:
+            loss_sum, n_valid, lse = torch.ops.ftk.lmhead_ce_fwd(hidden, weight, bias, targets)
+            ctx.save_for_backward(hidden, weight, bias, targets, lse, n_valid)
+        ctx.consumed = False
         # mean over valid rows (transformers fixed_cross_entropy, reduction="mean"); 0/0 -> NaN as in the reference
         return (loss_sum / n_valid.to(torch.float32)).reshape(())
 
     @staticmethod
     def backward(ctx, grad_out):
-        hidden, weight, bias, targets, lse, n_valid = ctx.saved_tensors
-        dH, dW, dbias = torch.ops.ftk.lmhead_ce_bwd(hidden, weight, bias, targets, lse, grad_out.reshape(1), n_valid,
-                                                    1.0, False)
+        if ctx.keep:
+            if ctx.consumed:
+                raise _lib.FtkError("the kept softmax numerators were consumed by the first backward "
+                                    "(use set_backward_mode('recompute') to backpropagate twice)")
+            hidden, weight, bias, targets, lse, n_valid, probs, cref = ctx.saved_tensors
+            dH, dW, dbias = torch.ops.ftk.lmhead_ce_bwd_kept(hidden, weight, bias is not None, targets, lse, probs, cref,
+                                                             grad_out.reshape(1), n_valid, 1.0, False)
+            ctx.consumed = True
+        else:
+            hidden, weight, bias, targets, lse, n_valid = ctx.saved_tensors
+            dH, dW, dbias = torch.ops.ftk.lmhead_ce_bwd(hidden, weight, bias, targets, lse, grad_out.reshape(1),
+                                                        n_valid, 1.0, False)
         return dH, dW, (dbias.to(bias.dtype) if bias is not None else None), None
 
 
 def fused_lmhead_ce(hidden: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor],
                     targets: torch.Tensor) -> torch.Tensor:
     """Mean causal-LM cross-entropy of logits = hidden @ weight.T (+ bias) against already shifted targets
-    (-100 = ignore).  hidden [M,d] bf16, weight [V,d] bf16.  Differentiable; the logits never reach HBM."""
+    (-100 = ignore).  hidden [M,d] bf16, weight [V,d] bf16.  Differentiable; the logits never reach HBM
+    (see ``set_backward_mode`` for the opt-in mode that keeps bf16 softmax numerators instead of recomputing)."""
     return _FusedLmHeadCE.apply(hidden, weight, bias, targets)

@@ -232,3 +232,48 @@ def test_hot_path_replays_from_a_cuda_graph(cuda_dev):
     torch.cuda.synchronize()
     assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1])
     assert torch.equal(got[2], want[2]) and torch.equal(got[3], want[3])
+
+
+@pytest.mark.parametrize("M,d,V,bias", [(128, 64, 256, False), (300, 64, 777, True), (1000, 256, 5003, True),
+                                        (2048, 768, 50257, False)])
+def test_keep_mode_parity(cuda_dev, M, d, V, bias):
+    """Opt-in mode: the forward keeps bf16 softmax numerators, the backward has no recompute GEMM.
+    Same oracle, same tolerances; loss and lse must equal the default path's bit for bit."""
+    H, W, b, t = mk(M, d, V, bias=bias, seed=M)
+    want = O.lmhead_ce_reference(H, W, b, t)
+    Hc, Wc, tc = H.cuda(), W.cuda(), t.cuda()
+    bc = None if b is None else b.cuda()
+    ls0, nv0, lse0 = torch.ops.ftk.lmhead_ce_fwd(Hc, Wc, bc, tc)
+    ls, nv, lse, probs, cref = torch.ops.ftk.lmhead_ce_fwd_keep(Hc, Wc, bc, tc)
+    assert int(nv) == int(nv0) == want["n_valid"]
+    assert abs(float(ls) / int(nv) - float(want["loss"])) <= LOSS_RTOL * abs(float(want["loss"]))
+    assert float((lse - lse0).abs().max()) < 1e-5
+    go = torch.tensor([0.5], device="cuda")
+    dH, dW, db = torch.ops.ftk.lmhead_ce_bwd_kept(Hc, Wc, bias, tc, lse, probs, cref, go, nv, 1.0, True)
+    torch.cuda.synchronize()
+    assert O.rel_err(dH.float(), 0.5 * want["dH"]) < GRAD_RTOL
+    assert O.rel_err(dW, 0.5 * want["dW"]) < GRAD_RTOL
+    if bias:
+        assert O.rel_err(db, 0.5 * want["dbias"]) < GRAD_RTOL
+    assert float(dH[t == -100].abs().max()) == 0.0
+
+
+def test_keep_mode_autograd_and_large_logits(cuda_dev):
+    """Through fused_lmhead_ce with set_backward_mode("keep"); logits spread over +-60 (a trained model's range and
+    beyond): the running-maximum reference keeps every exponent <= 0, so nothing overflows or loses the top tokens."""
+    from kubernetes_cloud_b200 import ops
+    H, W, _, t = mk(512, 128, 3001, seed=77, wstd=0.5)  # logits ~ N(0, 5.7): max |z| around 25
+    H[:7] *= 2.5                                         # a few rows with |z| up to ~60
+    want = O.lmhead_ce_reference(H, W, None, t)
+    ops.set_backward_mode("keep")
+    try:
+        Hc, Wc = H.cuda().requires_grad_(True), W.cuda().requires_grad_(True)
+        loss = ops.fused_lmhead_ce(Hc, Wc, None, t.cuda())
+        loss.backward()
+        with pytest.raises(Exception):
+            loss.backward()  # numerators are consumed by the first backward
+    finally:
+        ops.set_backward_mode("recompute")
+    assert abs(float(loss) - float(want["loss"])) <= LOSS_RTOL * abs(float(want["loss"]))
+    assert O.rel_err(Hc.grad.float(), want["dH"]) < GRAD_RTOL
+    assert O.rel_err(Wc.grad.float(), want["dW"]) < GRAD_RTOL
