@@ -135,8 +135,8 @@ struct FwdEpi {
       const float neg = -m_new * kLog2e;
       float acc = 0.f;
 #pragma unroll
-      for (int j = 0; j < 32; ++j) acc += exp2f(fmaf(v[j], kLog2e, neg));
-      st.s = st.s * exp2f(fmaf(st.m, kLog2e, neg)) + acc;  // exp2(-inf) = 0 on the first group
+      for (int j = 0; j < 32; ++j) acc += fast_exp2(fmaf(v[j], kLog2e, neg));
+      st.s = st.s * fast_exp2(fmaf(st.m, kLog2e, neg)) + acc;  // exp2(-inf) = 0 on the first group
       st.m = m_new;
     }
   }
@@ -212,8 +212,8 @@ struct DzEpi {
         uint32_t w[16];
 #pragma unroll
         for (int j = 0; j < 32; j += 2) {
-          float g0 = exp2f(fmaf(v[j], kLog2e, st.l2));
-          float g1 = exp2f(fmaf(v[j + 1], kLog2e, st.l2));
+          float g0 = fast_exp2(fmaf(v[j], kLog2e, st.l2));
+          float g1 = fast_exp2(fmaf(v[j + 1], kLog2e, st.l2));
           g0 = (c0 + j == st.tgt) ? g0 - 1.f : g0;
           g1 = (c0 + j + 1 == st.tgt) ? g1 - 1.f : g1;
           g0 = (c0 + j < p.V) ? g0 * st.sc : 0.f;  // pad columns [V, ld) are written as zeros
@@ -284,35 +284,35 @@ struct FwdKeepEpi {
     // ---- pass 1 over the accumulator: row maximum of this tile (and the target logit)
     float tmax = -INFINITY;
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
-      const int col0 = n0 + c * 32;
+    for (int c = 0; c < BN / 64; ++c) {
+      const int col0 = n0 + c * 64;
       if (col0 >= p.V) break;  // warp-uniform
-      float v[32];
-      tmem_ld32(taddr + c * 32, v);
+      float v[64];
+      tmem_ld64(taddr + c * 64, v);
       tmem_ld_wait();
       if (p.bias != nullptr) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
+        for (int j = 0; j < 64; ++j)
           if (col0 + j < p.V) v[j] += __bfloat162float(__ldg(p.bias + col0 + j));
       }
-      if (col0 + 32 > p.V) {
+      if (col0 + 64 > p.V) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
+        for (int j = 0; j < 64; ++j)
           if (col0 + j >= p.V) v[j] = -INFINITY;
       }
-      if (st.tgt >= col0 && st.tgt < col0 + 32) {
+      if (st.tgt >= col0 && st.tgt < col0 + 64) {
         const int jj = st.tgt - col0;
 #pragma unroll
-        for (int j = 0; j < 32; ++j)
+        for (int j = 0; j < 64; ++j)
           if (j == jj) st.zt = v[j];
         st.has = true;
       }
 #pragma unroll
-      for (int j = 0; j < 32; ++j) tmax = fmaxf(tmax, v[j]);
+      for (int j = 0; j < 64; ++j) tmax = fmaxf(tmax, v[j]);
     }
     const float m_new = fmaxf(st.m, tmax);  // finite: column n0 < V is real
     const float neg = -m_new * kLog2e;
-    st.s *= exp2f(fmaf(st.m, kLog2e, neg));  // exp2(-inf) = 0 on the first tile of a unit
+    st.s *= fast_exp2(fmaf(st.m, kLog2e, neg));  // exp2(-inf) = 0 on the first tile of a unit
     st.m = m_new;
     if (st.row < p.M) p.cref[static_cast<size_t>(n0 / BN) * p.Mpad + st.row] = m_new;
     // ---- pass 2: numerators relative to m_new, summed in fp32 and stored in bf16
@@ -326,31 +326,32 @@ struct FwdKeepEpi {
       uint8_t* buf = warp_buf + (st.nstore & 1) * 4096;
       if (cx.lane == 0) tma_store_wait_read<1>();
       __syncwarp();
+      float v[64];
+      tmem_ld64(taddr + g * 64, v);
+      tmem_ld_wait();
+      if (p.bias != nullptr) {
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int c0 = col0 + h * 32;
-        float v[32];
-        tmem_ld32(taddr + g * 64 + h * 32, v);
-        tmem_ld_wait();
-        if (p.bias != nullptr) {
+        for (int j = 0; j < 64; ++j)
+          if (col0 + j < p.V) v[j] += __bfloat162float(__ldg(p.bias + col0 + j));
+      }
+      const bool tail = col0 + 64 > p.V;  // warp-uniform: only the last real group needs the column predicate
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (c0 + j < p.V) v[j] += __bfloat162float(__ldg(p.bias + c0 + j));
-        }
-        uint32_t w[16];
+      for (int qq = 0; qq < 8; ++qq) {
+        uint32_t w[4];
 #pragma unroll
-        for (int j = 0; j < 32; j += 2) {
-          const float e0 = (c0 + j < p.V) ? exp2f(fmaf(v[j], kLog2e, neg)) : 0.f;
-          const float e1 = (c0 + j + 1 < p.V) ? exp2f(fmaf(v[j + 1], kLog2e, neg)) : 0.f;
+        for (int e = 0; e < 4; ++e) {
+          const int j = qq * 8 + 2 * e;
+          float e0 = fast_exp2(fmaf(v[j], kLog2e, neg));
+          float e1 = fast_exp2(fmaf(v[j + 1], kLog2e, neg));
+          if (tail) {
+            e0 = (col0 + j < p.V) ? e0 : 0.f;
+            e1 = (col0 + j + 1 < p.V) ? e1 : 0.f;
+          }
           acc += e0 + e1;
-          w[j >> 1] = pack_bf16x2(e0, e1);
+          w[e] = pack_bf16x2(e0, e1);
         }
-#pragma unroll
-        for (int qq = 0; qq < 4; ++qq) {
-          const int c = h * 4 + qq;
-          uint4* dst = reinterpret_cast<uint4*>(buf + cx.lane * 128 + ((c ^ (cx.lane & 7)) << 4));
-          *dst = make_uint4(w[4 * qq], w[4 * qq + 1], w[4 * qq + 2], w[4 * qq + 3]);
-        }
+        uint4* dst = reinterpret_cast<uint4*>(buf + cx.lane * 128 + ((qq ^ (cx.lane & 7)) << 4));
+        *dst = make_uint4(w[0], w[1], w[2], w[3]);
       }
       fence_async_shared();
       __syncwarp();
@@ -752,36 +753,55 @@ __global__ void __launch_bounds__(128) dbias_kernel(const __nv_bfloat16* __restr
 
 
 // Kept numerators -> dZ in place: dZ[r, c] = e[r, c] * exp(cref[tile(c)][r] - lse[r]) * scale_r - (c == target_r) * scale_r,
-// scale_r = 0 on ignored rows.  HBM-bound: one 16-byte load and store per thread.
+// scale_r = 0 on ignored rows.  HBM-bound.  One block per row: the per-tile factors of the row go to shared memory
+// once, then the row streams through in 16-byte accesses, four independent loads per thread in flight.
 __global__ void __launch_bounds__(256) probs_to_dz_kernel(__nv_bfloat16* __restrict__ probs,
                                                           const float* __restrict__ cref,
                                                           const float* __restrict__ lse,
                                                           const int64_t* __restrict__ targets, int rows, int V, int ld,
-                                                          int Mpad, int tile_cols, float scale,
+                                                          int Mpad, int n_tiles, float scale,
                                                           const float* __restrict__ scale_dev,
                                                           const int32_t* __restrict__ nvalid_dev) {
-  const int r = blockIdx.y;
-  const int c8 = (blockIdx.x * 256 + threadIdx.x) * 8;
-  if (r >= rows || c8 >= ld) return;
+  extern __shared__ float s_f[];  // n_tiles factors
+  const int r = blockIdx.x;
+  if (r >= rows) return;
   const int tgt = static_cast<int>(targets[r]);
   float sc = scale;
   if (scale_dev != nullptr) sc *= __ldg(scale_dev);
   if (nvalid_dev != nullptr) sc /= static_cast<float>(__ldg(nvalid_dev));
   if (tgt < 0) sc = 0.f;
-  const float f = exp2f((__ldg(cref + static_cast<size_t>(c8 / tile_cols) * Mpad + r) - __ldg(lse + r)) * kLog2e) * sc;
-  uint4* ptr = reinterpret_cast<uint4*>(probs + static_cast<size_t>(r) * ld + c8);
-  const uint4 in = __ldcs(ptr);
-  const uint32_t iw[4] = {in.x, in.y, in.z, in.w};
-  uint32_t ow[4];
+  const float l = __ldg(lse + r);
+  for (int t = threadIdx.x; t < n_tiles; t += 256)
+    s_f[t] = exp2f((__ldg(cref + static_cast<size_t>(t) * Mpad + r) - l) * kLog2e) * sc;
+  __syncthreads();
+  uint4* row = reinterpret_cast<uint4*>(probs + static_cast<size_t>(r) * ld);
+  const int nvec = ld / 8;  // ld is a multiple of 64
+  for (int i0 = threadIdx.x; i0 < nvec; i0 += 256 * 4) {
+    uint4 in[4];
 #pragma unroll
-  for (int e = 0; e < 4; ++e) {
-    const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&iw[e]);
-    float a = __low2float(h) * f, b = __high2float(h) * f;
-    if (c8 + 2 * e == tgt) a -= sc;
-    if (c8 + 2 * e + 1 == tgt) b -= sc;
-    ow[e] = pack_bf16x2(a, b);
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * 256;
+      if (i < nvec) in[u] = __ldcs(row + i);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * 256;
+      if (i >= nvec) break;
+      const int c8 = i * 8;
+      const float f = s_f[c8 >> 8];  // 256-column tiles
+      const uint32_t iw[4] = {in[u].x, in[u].y, in[u].z, in[u].w};
+      uint32_t ow[4];
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&iw[e]);
+        float a = __low2float(h) * f, b = __high2float(h) * f;
+        if (c8 + 2 * e == tgt) a -= sc;
+        if (c8 + 2 * e + 1 == tgt) b -= sc;
+        ow[e] = pack_bf16x2(a, b);
+      }
+      row[i] = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+    }
   }
-  *ptr = make_uint4(ow[0], ow[1], ow[2], ow[3]);
 }
 
 // ------------------------------------------------------------------------------------------------ host side
@@ -1299,17 +1319,10 @@ extern "C" int ftk_lmhead_ce_bwd_kept(const void* H, const void* W, const int64_
   const int64_t ld = dz_pitch(V);
   if (dbias != nullptr && !accumulate) FTK_CUDA_CHECK(cudaMemsetAsync(dbias, 0, sizeof(float) * V, st));
   {
-    dim3 grid(ceil_div(ld, 256 * 8), static_cast<unsigned>(M));
-    FTK_REQUIRE(M <= 65535 * 64, "ftk_lmhead_ce_bwd_kept: M too large");
-    // gridDim.y is limited to 65535: fold rows beyond that into several launches
-    for (int64_t r0 = 0; r0 < M; r0 += 65535) {
-      const int rows = static_cast<int>(M - r0 < 65535 ? M - r0 : 65535);
-      grid.y = rows;
-      probs_to_dz_kernel<<<grid, 256, 0, st>>>(static_cast<__nv_bfloat16*>(probs) + static_cast<size_t>(r0) * ld,
-                                               cref + r0, lse + r0, targets + r0, rows, V, static_cast<int>(ld),
-                                               static_cast<int>(round_up(M, 256)), 256, grad_scale, grad_scale_dev,
-                                               n_valid_dev);
-    }
+    const int n_tiles = ceil_div(V, 256);
+    probs_to_dz_kernel<<<static_cast<unsigned>(M), 256, n_tiles * sizeof(float), st>>>(
+        static_cast<__nv_bfloat16*>(probs), cref, lse, targets, static_cast<int>(M), V, static_cast<int>(ld),
+        static_cast<int>(round_up(M, 256)), n_tiles, grad_scale, grad_scale_dev, n_valid_dev);
     FTK_CUDA_CHECK(cudaGetLastError());
   }
   if (cta_group() == 2 && di.sm_count >= 2)

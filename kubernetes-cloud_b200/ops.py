@@ -223,7 +223,7 @@ def lmhead_ce_bwd_kept(H: torch.Tensor, W: torch.Tensor, has_bias: bool, targets
                                                _lib.FTK_F32 if dw_fp32 else _lib.FTK_BF16, 0,
                                                dbias.data_ptr() if has_bias else 0, _stream(H))
     _lib.check(rc, "ftk_lmhead_ce_bwd_kept")
-    _launches += 3 + (1 if has_bias else 0) + (M + 65534) // 65535 - 1
+    _launches += 3 + (1 if has_bias else 0)
     return dH, dW, dbias
 
 

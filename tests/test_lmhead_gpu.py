@@ -239,6 +239,7 @@ def test_hot_path_replays_from_a_cuda_graph(cuda_dev):
 def test_keep_mode_parity(cuda_dev, M, d, V, bias):
     """Opt-in mode: the forward keeps bf16 softmax numerators, the backward has no recompute GEMM.
     Same oracle, same tolerances; loss and lse must equal the default path's bit for bit."""
+    from kubernetes_cloud_b200 import ops  # noqa: F401  (registers torch.ops.ftk.*)
     H, W, b, t = mk(M, d, V, bias=bias, seed=M)
     want = O.lmhead_ce_reference(H, W, b, t)
     Hc, Wc, tc = H.cuda(), W.cuda(), t.cuda()
