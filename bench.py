@@ -232,20 +232,27 @@ def main_gpu(args) -> None:
     state = {"dW": None}
     comm_launches = [0]
 
-    def hot_path(i: int, hidden: torch.Tensor, tok: torch.Tensor, idx: torch.Tensor, timed: bool):
+    def hot_path(i: int, hidden: torch.Tensor, tok: torch.Tensor, idx: torch.Tensor, timed: bool, keep: bool = False):
         ids, targets, mask, n_valid_rows = torch.ops.ftk.gather_windows(tok, idx, CTX, PAD_ID, True, True)
         if timed:
             e0 = torch.cuda.Event(enable_timing=True); e0.record(stream); ev_f0.append(e0)
         if sm_reserve and state["dW"] is not None:
             L.ftk_set_sm_reserve(sm_reserve)  # the previous step's all-reduce runs beside this forward
-        loss_sum, n_valid, lse = torch.ops.ftk.lmhead_ce_fwd(hidden, W, None, targets.view(-1))
+        if keep:
+            loss_sum, n_valid, lse, probs, cref = torch.ops.ftk.lmhead_ce_fwd_keep(hidden, W, None, targets.view(-1))
+        else:
+            loss_sum, n_valid, lse = torch.ops.ftk.lmhead_ce_fwd(hidden, W, None, targets.view(-1))
         if sm_reserve:
             L.ftk_set_sm_reserve(0)
         if timed:
             e1 = torch.cuda.Event(enable_timing=True); e1.record(stream); ev_f1.append(e1)
         if handle is not None and state["dW"] is not None:
             _lib.check(L.ftk_dp_join(handle, stream.cuda_stream), "ftk_dp_join")  # previous dW reduce must be done
-        dH, dW, _ = torch.ops.ftk.lmhead_ce_bwd(hidden, W, None, targets.view(-1), lse, None, n_valid, 1.0, False)
+        if keep:
+            dH, dW, _ = torch.ops.ftk.lmhead_ce_bwd_kept(hidden, W, False, targets.view(-1), lse, probs, cref, None,
+                                                         n_valid, 1.0, False)
+        else:
+            dH, dW, _ = torch.ops.ftk.lmhead_ce_bwd(hidden, W, None, targets.view(-1), lse, None, n_valid, 1.0, False)
         if timed:
             e2 = torch.cuda.Event(enable_timing=True); e2.record(stream); ev_b1.append(e2)
         state["dW"] = dW
@@ -373,6 +380,21 @@ def main_gpu(args) -> None:
     bwd_ms = sum(a.elapsed_time(b) for a, b in zip(ev_f1, ev_b1)) / args.steps
     loss_val = float(loss_sum) / max(int(n_valid), 1)
 
+    # ================= the same leg in the opt-in keep-numerators mode (not the headline) ==========
+    for i in range(args.warmup):
+        hot_path(i, H, tokens, idx_dev[i % nb], False, keep=True)
+    finish_comm()
+    barrier()
+    k0 = torch.cuda.Event(enable_timing=True)
+    k1 = torch.cuda.Event(enable_timing=True)
+    k0.record(stream)
+    for i in range(args.steps):
+        hot_path(args.warmup + i, H, tokens, idx_dev[(args.warmup + i) % nb], False, keep=True)
+    finish_comm()
+    k1.record(stream)
+    barrier()
+    keep_ms = max_over_ranks(k0.elapsed_time(k1)) / args.steps
+
     # ================= end-to-end leg: host buffers in, loss out, copies inside the timed region =================
     copy_stream = torch.cuda.Stream(dev)
     stage_tok = [torch.empty(BATCH * CTX, dtype=torch.int16, device=dev) for _ in range(2)]
@@ -471,6 +493,10 @@ def main_gpu(args) -> None:
                            "frac": adam_gbs / peaks["hbm"], "ms": adam_ms,
                            "note": "grad-norm + clip + fused AdamW on the 103M-element bf16 lm_head bucket, 30 B/param; "
                                    "not part of the timed step"},
+        "keep_mode": {"ms_per_step": keep_ms, "value": world * M / (keep_ms / 1e3), "unit": "tokens/s",
+                      "fused_algorithmic_tflops": 3 * flops_fwd / (keep_ms / 1e3) / 1e12,
+                      "note": "opt-in ops.set_backward_mode('keep'): the forward also stores bf16 softmax numerators "
+                              "(1.65 GB here) and the backward skips the logit recompute; not used for `value`"},
         "e2e": {"value": e2e_value, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms / args.steps,
                 "note": "token windows + hidden states from pinned host memory each step, loss and count read back"},
