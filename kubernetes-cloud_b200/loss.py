@@ -61,5 +61,18 @@ class ModifiedTrainerMixin:
         self.report_idx = getattr(self, "report_idx", 0) + 1
         gas = getattr(getattr(self, "args", None), "gradient_accumulation_steps", 1)
         if self.report_idx % (2 * gas) == 0 and getattr(self, "is_world_process_zero", lambda: True)():
-            print(f"\nLOSS: {loss:.3f}", file=sys.stderr, flush=True)  # FT.py:486-491
+            # FT.py:486-491 formats the loss tensor, which stalls the host until the GPU catches up.  Here the value
+            # goes to pinned memory with an asynchronous copy and the line printed is the previous report's value,
+            # whose copy has long finished: same output cadence, no pipeline bubble.
+            prev = getattr(self, "_loss_report", None)
+            if prev is not None:
+                buf, ev = prev
+                ev.synchronize()
+                print(f"\nLOSS: {float(buf):.3f}", file=sys.stderr, flush=True)
+            if loss.is_cuda:
+                buf = torch.empty((), dtype=torch.float32).pin_memory()
+                buf.copy_(loss.detach().float(), non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record()
+                self._loss_report = (buf, ev)
         return results

@@ -47,3 +47,22 @@ def epoch_batches(n_ctx: int, batch_size: int, seed: int = 42, shuffle: bool = T
         if drop_last and b.numel() < batch_size:
             return
         yield b
+
+
+def sampler_epoch_order(train_indices: torch.Tensor, seed: int, epoch: int, rank: int, world: int,
+                        shuffle: bool = True) -> torch.Tensor:
+    """The order in which HF Trainer's ``DistributedSampler`` (world > 1, ``seed=args.seed``) walks the reference's
+    ``train_dataset`` in a given epoch, composed with the ``random_split`` permutation behind that Subset:
+    positions = randperm(n) from a generator seeded ``seed + epoch`` (or 0..n-1 without shuffle), padded by wrap-around
+    to a multiple of ``world``, sliced ``rank::world`` (torch/utils/data/distributed.py:107-134), then mapped through
+    ``train_indices`` (FT.py:761).  For world == 1 the Trainer uses a RandomSampler seeded from the global RNG state
+    at that moment, which depends on how many draws model initialisation made and cannot be reproduced from the
+    flags alone; this function applies the same seeded rule there."""
+    n = train_indices.numel()
+    if shuffle:
+        g = torch.Generator()
+        g.manual_seed(seed + epoch)
+        pos = torch.randperm(n, generator=g)
+    else:
+        pos = torch.arange(n)
+    return train_indices[rank_slice(pos, rank, world)]

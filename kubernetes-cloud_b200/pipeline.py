@@ -19,15 +19,28 @@ from .ordering import rank_slice, train_order
 
 class DeviceBatcher:
     def __init__(self, ds: TokenizedDataset, batch_size: int, seed: int = 42, shuffle: bool = True, rank: int = 0,
-                 world: int = 1, shift_labels: bool = True, prefetch: int = 2, drop_last: bool = False):
+                 world: int = 1, shift_labels: bool = True, prefetch: int = 2, drop_last: bool = False,
+                 trainer_sampler: bool = False):
         if batch_size <= 0 or prefetch < 1:
             raise ValueError("batch_size and prefetch must be positive")
         self.ds, self.batch_size, self.seed, self.shuffle = ds, batch_size, seed, shuffle
         self.rank, self.world, self.shift_labels, self.prefetch, self.drop_last = rank, world, shift_labels, prefetch, drop_last
         self.stream = torch.cuda.Stream(ds.device)
         # FT.py:761: one permutation for the whole run (random_split happens once, before training)
-        self.order_host = rank_slice(train_order(len(ds), seed, shuffle), rank, world).contiguous()
-        self.order_dev = self.order_host.to(ds.device)  # 8 B per context, uploaded once
+        # trainer_sampler=True additionally re-draws the per-epoch DistributedSampler permutation the HF Trainer
+        # applies on top of it (ordering.sampler_epoch_order); the default walks the split order itself.
+        self.trainer_sampler = trainer_sampler
+        self._split = train_order(len(ds), seed, shuffle)
+        self.set_epoch(0)
+
+    def set_epoch(self, epoch: int) -> None:
+        if self.trainer_sampler:
+            from .ordering import sampler_epoch_order
+            order = sampler_epoch_order(self._split, self.seed, epoch, self.rank, self.world, shuffle=True)
+        else:
+            order = rank_slice(self._split, self.rank, self.world)
+        self.order_host = order.contiguous()
+        self.order_dev = self.order_host.to(self.ds.device)  # 8 B per context
 
     def batches_per_epoch(self) -> int:
         n = self.order_host.numel()

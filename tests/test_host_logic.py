@@ -138,3 +138,23 @@ def test_token_file_writer_and_validator(tmp_path):
     assert validate_token_file(p, T, pad_id=1000, eos_id=999).ok  # distinct pad: every context is masked by id
     with pytest.raises(ValueError):
         write_token_file(p, [70000], T, 0)
+
+
+def test_sampler_epoch_order_matches_distributed_sampler_over_the_split():
+    """world > 1: HF Trainer wraps the reference's Subset in DistributedSampler(seed=args.seed); reproduce its walk."""
+    from torch.utils.data import Subset, random_split
+    from torch.utils.data.distributed import DistributedSampler
+    from kubernetes_cloud_b200.ordering import sampler_epoch_order, train_order
+    n, seed = 37, 42
+    torch.manual_seed(seed)
+    train, _ = random_split(range(n), (n, 0))          # FT.py:739, :761
+    split = train_order(n, seed)
+    assert list(split) == list(train.indices)
+    for world in (2, 8):
+        for epoch in (0, 3):
+            for rank in range(world):
+                smp = DistributedSampler(train, num_replicas=world, rank=rank, seed=seed, shuffle=True)
+                smp.set_epoch(epoch)
+                want = [train[i] for i in smp]           # dataset items = context indices
+                got = sampler_epoch_order(split, seed, epoch, rank, world)
+                assert [int(v) for v in got] == want

@@ -278,3 +278,46 @@ def test_keep_mode_autograd_and_large_logits(cuda_dev):
     assert abs(float(loss) - float(want["loss"])) <= LOSS_RTOL * abs(float(want["loss"]))
     assert O.rel_err(Hc.grad.float(), want["dH"]) < GRAD_RTOL
     assert O.rel_err(Wc.grad.float(), want["dW"]) < GRAD_RTOL
+
+
+def test_trainer_mixin_reports_loss_without_stalling(cuda_dev, capsys):
+    """ModifiedTrainerMixin keeps the reference's LOSS: line (FT.py:486-491) every 2*GAS calls, printing the value
+    captured at the previous report through an asynchronous copy."""
+    import types
+    from transformers import GPTNeoConfig, GPTNeoForCausalLM
+    from kubernetes_cloud_b200.loss import ModifiedTrainerMixin
+    torch.manual_seed(0)
+    model = GPTNeoForCausalLM(GPTNeoConfig(vocab_size=300, hidden_size=64, num_layers=1, num_heads=2,
+                                           max_position_embeddings=64, attention_types=[[["global"], 1]],
+                                           window_size=16)).cuda().to(torch.bfloat16)
+
+    class T(ModifiedTrainerMixin):
+        args = types.SimpleNamespace(gradient_accumulation_steps=1)
+
+    tr = T()
+    ids = torch.randint(0, 300, (2, 64), device="cuda")
+    losses = []
+    for _ in range(4):
+        inputs = {"input_ids": ids, "attention_mask": torch.ones_like(ids, dtype=torch.bool), "labels": ids.clone()}
+        losses.append(float(tr.compute_loss(model, inputs).detach()))
+    err = capsys.readouterr().err
+    assert err.count("LOSS:") == 1                      # calls 2 and 4 report; the first has no earlier value to print
+    assert f"LOSS: {losses[1]:.3f}" in err              # the value captured at call 2
+
+
+def test_device_batcher_trainer_sampler_mode(cuda_dev, tmp_path):
+    from kubernetes_cloud_b200 import DeviceBatcher, TokenizedDataset, write_token_file
+    from kubernetes_cloud_b200.ordering import sampler_epoch_order, train_order
+    T, n = 32, 19
+    path = str(tmp_path / "t.tokens")
+    write_token_file(path, np.random.default_rng(1).integers(0, 90, size=n * T), T, pad_id=99)
+    ds = TokenizedDataset(path, T, pad_token_id=99, eos_token_id=99)
+    bt = DeviceBatcher(ds, batch_size=3, seed=42, rank=1, world=2, trainer_sampler=True)
+    for epoch in (0, 1):
+        bt.set_epoch(epoch)
+        want = sampler_epoch_order(train_order(n, 42), 42, epoch, 1, 2)
+        got = torch.cat([bt.index_list(k) for k in range(bt.batches_per_epoch())])
+        assert torch.equal(got, want)
+        first = next(iter(bt.epoch()))
+        raw = np.fromfile(path, dtype=np.uint16)
+        np.testing.assert_array_equal(first["input_ids"].cpu().numpy(), O.gather_numpy(raw, T, want[:3].numpy(), 99, True)[0])
