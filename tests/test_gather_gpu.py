@@ -116,3 +116,21 @@ def test_device_batcher_epoch_matches_reference_order(cuda_dev, tmp_path):
         assert torch.equal(resumed[0]["input_ids"], got[2]["input_ids"])
     ns = DeviceBatcher(ds, batch_size=8, shuffle=False)  # --no-shuffle keeps file order
     np.testing.assert_array_equal(ns.index_list(0).numpy(), np.arange(8))
+
+
+def test_random_shapes_against_c_oracle(cuda_dev):
+    """Randomised sweep over context lengths (all three kernel paths: T % 16 == 0, T % 4 == 0, scalar), batch sizes,
+    pad rules and both label forms; bit-exact against the C restatement."""
+    rng = np.random.default_rng(2024)
+    for case in range(60):
+        T = int(rng.choice([4, 8, 12, 16, 20, 33, 48, 64, 100, 127, 512, 520, 2048, 2052, 4100]))
+        n = int(rng.integers(1, 12))
+        B = int(rng.integers(1, 10))
+        pad = int(rng.integers(0, 4))
+        tok = rng.integers(0, 5, size=n * T, dtype=np.uint16)
+        idx = rng.integers(0, n, size=B)
+        pad_is_eos, shift = bool(rng.integers(0, 2)), bool(rng.integers(0, 2))
+        want = O.gather_c(tok, T, idx, pad, pad_is_eos, shift)
+        got = run_gpu(tok, T, idx, pad, pad_is_eos, shift)
+        for w, g in zip(want, got):
+            np.testing.assert_array_equal(w, g, err_msg=f"case {case}: T={T} n={n} B={B} pad={pad} eos={pad_is_eos} shift={shift}")
