@@ -321,3 +321,34 @@ def test_device_batcher_trainer_sampler_mode(cuda_dev, tmp_path):
         first = next(iter(bt.epoch()))
         raw = np.fromfile(path, dtype=np.uint16)
         np.testing.assert_array_equal(first["input_ids"].cpu().numpy(), O.gather_numpy(raw, T, want[:3].numpy(), 99, True)[0])
+
+
+def test_random_shapes_both_modes(cuda_dev, monkeypatch):
+    """Randomised small shapes (rows and vocabulary sizes that straddle tile edges, d any multiple of 64), both CTA
+    groupings, default (recompute) and keep modes, against the fp32 oracle."""
+    from kubernetes_cloud_b200 import ops  # noqa: F401
+    rng = np.random.default_rng(7)
+    for case in range(14):
+        M = int(rng.integers(1, 700))
+        d = 64 * int(rng.integers(1, 7))
+        V = int(rng.integers(2, 2500))
+        bias = bool(rng.integers(0, 2))
+        monkeypatch.setenv("FTK_CTA_GROUP", "1" if case % 3 == 0 else "2")
+        H, W, b, t = mk(M, d, V, seed=100 + case, bias=bias, frac_ignore=0.15)
+        if (t >= 0).sum() == 0:
+            t[0] = 0
+        want = O.lmhead_ce_reference(H, W, b, t)
+        tag = f"case {case}: M={M} d={d} V={V} bias={bias}"
+        loss, n_valid, lse, dH, dW, db = gpu_fwd_bwd(H, W, b, t)
+        assert n_valid == want["n_valid"], tag
+        assert abs(loss - float(want["loss"])) <= LOSS_RTOL * abs(float(want["loss"])), tag
+        assert O.rel_err(dH, want["dH"]) < GRAD_RTOL and O.rel_err(dW, want["dW"]) < GRAD_RTOL, tag
+        Hc, Wc, tc = H.cuda(), W.cuda(), t.cuda()
+        bc = None if b is None else b.cuda()
+        ls, nv, lse2, probs, cref = torch.ops.ftk.lmhead_ce_fwd_keep(Hc, Wc, bc, tc)
+        dH2, dW2, db2 = torch.ops.ftk.lmhead_ce_bwd_kept(Hc, Wc, bias, tc, lse2, probs, cref, None, nv, 1.0, False)
+        torch.cuda.synchronize()
+        assert float((lse2.cpu() - lse).abs().max()) < 1e-5, tag
+        assert O.rel_err(dH2.float(), want["dH"]) < GRAD_RTOL and O.rel_err(dW2.float(), want["dW"]) < GRAD_RTOL, tag
+        if bias:
+            assert O.rel_err(db, want["dbias"]) < GRAD_RTOL and O.rel_err(db2, want["dbias"]) < GRAD_RTOL, tag
