@@ -84,6 +84,7 @@ def test_hf_fixture(cuda_dev, golden_dir, name):
     bc = None if b is None else b.cuda().requires_grad_(True)
     loss = ops.fused_lmhead_ce(Hc, Wc, bc, targets.cuda())
     loss.backward()
+    loss = loss.detach()
     # against the oracle on the same bf16-rounded inputs: the stated tolerances
     want = O.lmhead_ce_reference(H, W, b, targets)
     assert abs(float(loss) - float(want["loss"])) <= LOSS_RTOL * abs(float(want["loss"]))
