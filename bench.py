@@ -160,6 +160,8 @@ def main_reference(args) -> None:
     if rank != 0:
         return
     import torch
+    # torchrun exports OMP_NUM_THREADS=1 to every rank; the CPU arm is rank 0 alone and should use the whole host
+    torch.set_num_threads(os.cpu_count() or 1)
     step = cpu_step_fn(1)
     for _ in range(max(args.warmup, 1)):
         step()
@@ -281,8 +283,10 @@ def main_gpu(args) -> None:
 
     # ================= bulk gather bandwidth (HBM roofline of G1; outside the step: one step's gather is 0.3 MB).
     # Measured first, on a GPU that is not yet power-capped by the GEMM phase: the kernel tracks the SM/L2 clock. ====
-    n_bulk = 4096 * 8  # 2^26 tokens per launch
-    big_idx = torch.randint(0, N_CTX_FILE, (n_bulk,), device=dev)
+    n_bulk = 4096 * 8  # 2^26 tokens per launch, each context of a 134 MB source read exactly once (a permutation):
+    # the source is larger than the 126 MB L2, so the 2 B/token read side is HBM traffic as well
+    big_tokens = torch.randint(0, VOCAB, (n_bulk * CTX,), device=dev, dtype=torch.int32).to(torch.int16)
+    big_idx = torch.randperm(n_bulk, device=dev)
 
     # The kernel is timed through the C ABI into preallocated outputs: going through the torch op would add four
     # fresh 0.1-0.5 GB allocations per call to the measurement (that path measured 4.3-4.7 TB/s for the same kernel).
@@ -292,7 +296,7 @@ def main_gpu(args) -> None:
     b_nv = torch.empty(n_bulk, dtype=torch.int32, device=dev)
 
     def bulk_launch():
-        _lib.check(L.ftk_gather_windows(tokens.data_ptr(), N_CTX_FILE, CTX, big_idx.data_ptr(), n_bulk, PAD_ID, 1, 1,
+        _lib.check(L.ftk_gather_windows(big_tokens.data_ptr(), n_bulk, CTX, big_idx.data_ptr(), n_bulk, PAD_ID, 1, 1,
                                         b_ids.data_ptr(), b_lab.data_ptr(), b_msk.data_ptr(), b_nv.data_ptr(),
                                         stream.cuda_stream), "ftk_gather_windows")
 
@@ -310,13 +314,13 @@ def main_gpu(args) -> None:
         return 19.0 * n_bulk * CTX / (g0.elapsed_time(g1) / 10 / 1e3) / 1e9
 
     gather_gbs = bulk_gather_gbs()
-    os.environ["FTK_GATHER_VARIANT"] = "direct"
+    _lib.set_option("gather_variant", 1)
     gather_direct_gbs = bulk_gather_gbs()
-    del os.environ["FTK_GATHER_VARIANT"]
-    os.environ["FTK_GATHER_STORES"] = "plain"
+    _lib.set_option("gather_variant", 0)
+    _lib.set_option("gather_stores", 2)
     gather_plain_gbs = bulk_gather_gbs()
-    del os.environ["FTK_GATHER_STORES"]
-    del b_ids, b_lab, b_msk, b_nv
+    _lib.set_option("gather_stores", 0)
+    del b_ids, b_lab, b_msk, b_nv, big_tokens
 
     # ================= optimizer step on the lm_head / wte bucket (HBM roofline) =================
     n_par = VOCAB * D_MODEL
@@ -487,7 +491,8 @@ def main_gpu(args) -> None:
                            "note": "algorithmic 6MVd over forward + backward time"},
         "roofline_gather": {"bound": "hbm", "achieved": gather_gbs, "peak": peaks["hbm"], "unit": "GB/s",
                             "frac": gather_gbs / peaks["hbm"],
-                            "note": "bulk launch of 2^26 tokens, 19 B/token, streaming stores, timed through the C ABI",
+                            "note": "bulk launch of 2^26 tokens drawn once each from a 134 MB source (> L2), 19 B/token, "
+                                    "streaming stores, timed through the C ABI",
                             "direct_variant_gbs": gather_direct_gbs, "plain_stores_gbs": gather_plain_gbs,},
         "roofline_adamw": {"bound": "hbm", "achieved": adam_gbs, "peak": peaks["hbm"], "unit": "GB/s",
                            "frac": adam_gbs / peaks["hbm"], "ms": adam_ms,

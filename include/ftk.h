@@ -51,6 +51,22 @@ int ftk_version(void);
 const char* ftk_last_error(void);
 
 /*
+ * Process-wide tuning options. Each is one atomic integer read at launch time; nothing is read from the
+ * environment. No counterpart in the reference.
+ *   FTK_OPT_CTA_GROUP       2 (default): tcgen05 cta_group::2, a CTA pair shares one 256-row tile; 1: single CTAs
+ *   FTK_OPT_GATHER_VARIANT  0 (default): pick by shape; 1: the direct (no shared memory) kernel where it applies
+ *   FTK_OPT_GATHER_STORES   0 (default): streaming stores for launches of >= 4 M tokens; 1: always; 2: never
+ *   FTK_OPT_SM_RESERVE      n in [0, 64]: SMs the persistent lm_head kernels launched from now on leave idle
+ *                           (same as ftk_set_sm_reserve)
+ */
+#define FTK_OPT_CTA_GROUP 0
+#define FTK_OPT_GATHER_VARIANT 1
+#define FTK_OPT_GATHER_STORES 2
+#define FTK_OPT_SM_RESERVE 3
+#define FTK_OPT_COUNT_ 4
+int ftk_set_option(int32_t key, int32_t value);
+
+/*
  * Window gather + label/mask construction, one launch per micro-batch.
  * Replaces TokenizedDataset.load (FT.py:662-692: slice, uint16->int64 widen,
  * mask rule), collector (FT.py:1030-1035: three stacks) and the label fill of

@@ -38,6 +38,7 @@ SIGNATURES = {
     "ftk_lmhead_ce_bwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32,
                                     c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_void_p,
                                     c_void_p, c_size_t, c_void_p]),
+    "ftk_set_option": (c_int32, [c_int32, c_int32]),
     "ftk_set_sm_reserve": (c_int32, [c_int32]),
     "ftk_dp_unique_id": (c_int32, [c_void_p]),
     "ftk_dp_init": (c_int32, [c_void_p, c_int32, c_int32, POINTER(c_void_p)]),
@@ -50,6 +51,9 @@ SIGNATURES = {
     "ftk_adamw_step": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_int32, c_int32, c_float,
                                  c_float, c_float, c_float, c_float, c_int64, c_float, c_void_p, c_void_p]),
 }
+
+
+OPTIONS = {"cta_group": 0, "gather_variant": 1, "gather_stores": 2, "sm_reserve": 3}  # FTK_OPT_* in include/ftk.h
 
 
 class FtkError(RuntimeError):
@@ -92,3 +96,9 @@ def check(rc: int, what: str) -> None:
     if rc != 0:
         msg = lib().ftk_last_error()
         raise FtkError(f"{what} failed ({rc}): {msg.decode() if msg else ''}")
+
+
+def set_option(name: str, value: int) -> None:
+    """ftk_set_option by name: "cta_group" (1|2), "gather_variant" (0 auto|1 direct), "gather_stores"
+    (0 auto|1 streaming|2 plain), "sm_reserve" (0..64)."""
+    check(lib().ftk_set_option(OPTIONS[name], int(value)), f"ftk_set_option({name})")

@@ -165,11 +165,21 @@ extern "C" int ftk_dp_init(const void* id128_host, int32_t rank, int32_t world, 
     free(dp);
     return ftk::fail(FTK_ENCCL, "ncclCommInitRank failed: %s", api->GetErrorString(r));
   }
+  // from here on a failure must give back what was created: one exit path
   int lo = 0, hi = 0;
-  FTK_CUDA_CHECK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-  FTK_CUDA_CHECK(cudaStreamCreateWithPriority(&dp->comm_stream, cudaStreamNonBlocking, hi));
-  FTK_CUDA_CHECK(cudaEventCreateWithFlags(&dp->ev_ready, cudaEventDisableTiming));
-  FTK_CUDA_CHECK(cudaEventCreateWithFlags(&dp->ev_done, cudaEventDisableTiming));
+  cudaError_t e = cudaDeviceGetStreamPriorityRange(&lo, &hi);
+  if (e == cudaSuccess) e = cudaStreamCreateWithPriority(&dp->comm_stream, cudaStreamNonBlocking, hi);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&dp->ev_ready, cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&dp->ev_done, cudaEventDisableTiming);
+  if (e != cudaSuccess) {
+    if (dp->ev_done != nullptr) cudaEventDestroy(dp->ev_done);
+    if (dp->ev_ready != nullptr) cudaEventDestroy(dp->ev_ready);
+    if (dp->comm_stream != nullptr) cudaStreamDestroy(dp->comm_stream);
+    api->CommDestroy(dp->comm);
+    free(dp);
+    return ftk::fail(FTK_ECUDA, "ftk_dp_init: creating the communication stream / events failed: %s",
+                     cudaGetErrorString(e));
+  }
   *out = dp;
   return FTK_OK;
 }
@@ -178,6 +188,7 @@ extern "C" int ftk_dp_allreduce(ftk_dp_t* dp, void* buf, size_t count, int32_t d
                                 void* ready_stream) {
   FTK_REQUIRE(dp && buf, "ftk_dp_allreduce: null pointer argument");
   FTK_REQUIRE(dtype == FTK_BF16 || dtype == FTK_F32, "ftk_dp_allreduce: bad dtype %d", dtype);
+  FTK_REQUIRE((reinterpret_cast<uintptr_t>(buf) & 15) == 0, "ftk_dp_allreduce: buffer %p is not 16-byte aligned", buf);
   if (count == 0) return FTK_OK;
   // the bucket is ready once everything issued so far on ready_stream has run
   FTK_CUDA_CHECK(cudaEventRecord(dp->ev_ready, static_cast<cudaStream_t>(ready_stream)));

@@ -38,4 +38,8 @@ struct DeviceInfo {
 };
 int get_device_info(DeviceInfo* out);  // current device; FTK_OK or error
 
+// Process-wide tuning options (ftk_set_option): read with a relaxed atomic load on every launch, never from the
+// environment.
+int option(int key);
+
 }  // namespace ftk

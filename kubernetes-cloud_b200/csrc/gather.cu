@@ -261,15 +261,14 @@ extern "C" int ftk_gather_windows(const uint16_t* tokens, int64_t n_ctx, int32_t
                          ((reinterpret_cast<uintptr_t>(labels) & 31) == 0) &&
                          ((reinterpret_cast<uintptr_t>(mask) & 31) == 0);
   // T % 16 == 0: the shared-memory staged kernel (measured 4-5 % faster on B200); T % 4 == 0: the direct kernel;
-  // anything else: the scalar path. FTK_GATHER_VARIANT=direct forces the direct kernel where it applies.
+  // anything else: the scalar path. ftk_set_option(FTK_OPT_GATHER_VARIANT, 1) forces the direct kernel where it applies.
   // Outputs too large to stay in L2 (>= 4 M tokens, 80 MB) leave through streaming stores (st.global.cs), which
   // measured +11 % on a 2^26-token launch; small batches use plain stores so the consumers find them in L2.
-  // FTK_GATHER_STORES=cs|plain overrides.
-  const char* variant = getenv("FTK_GATHER_VARIANT");
-  const bool want_direct = (variant != nullptr && variant[0] == 'd');
-  const char* stores = getenv("FTK_GATHER_STORES");
+  // FTK_OPT_GATHER_STORES overrides.
+  const bool want_direct = ftk::option(FTK_OPT_GATHER_VARIANT) == 1;
+  const int stores = ftk::option(FTK_OPT_GATHER_STORES);
   bool cs = static_cast<int64_t>(B) * T >= (int64_t(1) << 22);
-  if (stores != nullptr) cs = (stores[0] == 'c');
+  if (stores != 0) cs = (stores == 1);
   if (T % 4 == 0 && aligned32 && (want_direct || T % 16 != 0)) {
     const int64_t n_pieces = static_cast<int64_t>(B) * ((T + kPiece - 1) / kPiece);
     const int64_t blocks = (n_pieces + kThreads / 32 - 1) / (kThreads / 32);

@@ -670,7 +670,7 @@ __global__ void __launch_bounds__(256) fwd_finalize_kernel(const float* __restri
                                                            const float* __restrict__ psum,
                                                            const float* __restrict__ ztgt,
                                                            const int64_t* __restrict__ targets, int M, int Mpad,
-                                                           int n_chunks, float* __restrict__ lse,
+                                                           int V, int n_chunks, float* __restrict__ lse,
                                                            float* __restrict__ blk_loss, int* __restrict__ blk_cnt,
                                                            unsigned int* __restrict__ ticket,
                                                            float* __restrict__ loss_sum, int* __restrict__ n_valid) {
@@ -691,8 +691,11 @@ __global__ void __launch_bounds__(256) fwd_finalize_kernel(const float* __restri
     }
     const float l = gm + log2f(s) * kLn2;
     lse[row] = l;
-    if (targets[row] >= 0) {
-      loss = l - ztgt[row];
+    const int64_t tg = targets[row];
+    if (tg >= 0) {
+      // a target beyond the vocabulary matched no column, so ztgt[row] was never written: poison the loss
+      // (torch's cross_entropy raises a device assert here) instead of reading stale scratch
+      loss = (tg < V) ? l - ztgt[row] : __int_as_float(0x7fc00000);
       cnt = 1;
     }
   }
@@ -837,13 +840,7 @@ int make_tmap(CUtensorMap* tm, const void* base, uint64_t dim0, uint64_t dim1, u
   const cuuint64_t strides[1] = {pitch_bytes};
   const cuuint32_t box[2] = {box0, box1};
   const cuuint32_t estr[2] = {1, 1};
-  CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
-  if (const char* e = getenv("FTK_L2_PROMO")) {  // experiment knob: 0 none, 1 64 B, 2 128 B, 3 256 B
-    const int v = atoi(e);
-    promo = v == 0 ? CU_TENSOR_MAP_L2_PROMOTION_NONE
-                   : v == 1 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B
-                            : v == 2 ? CU_TENSOR_MAP_L2_PROMOTION_L2_128B : CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
-  }
+  const CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_L2_256B;  // 64 B / 128 B / none measured the same
   const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
                          CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, promo,
                          CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -851,9 +848,9 @@ int make_tmap(CUtensorMap* tm, const void* base, uint64_t dim0, uint64_t dim1, u
   return FTK_OK;
 }
 
-// SMs the persistent kernels leave idle (ftk_set_sm_reserve): room for a concurrent NCCL kernel, whose CTAs cannot
+// SMs the persistent kernels leave idle (FTK_OPT_SM_RESERVE): room for a concurrent NCCL kernel, whose CTAs cannot
 // share an SM with ours (registers) and would otherwise wait for a whole GEMM to finish.
-int g_sm_reserve = 0;
+inline int sm_reserve() { return ftk::option(FTK_OPT_SM_RESERVE); }
 
 template <int kCG, int BN, int kStages, bool kAMN, bool kBMN, class Epi>
 int launch_umma(const CUtensorMap& tmA, const CUtensorMap& tmB, const Sched& sc, const typename Epi::Params& ep,
@@ -867,7 +864,7 @@ int launch_umma(const CUtensorMap& tmA, const CUtensorMap& tmB, const Sched& sc,
     FTK_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(L::BYTES)));
     attr_done[dev & 63] = true;
   }
-  int usable = sm_count - g_sm_reserve;
+  int usable = sm_count - sm_reserve();
   if (usable < kCG) usable = kCG;
   int n_cl = usable / kCG;
   if (n_cl > sc.n_units) n_cl = sc.n_units;
@@ -888,11 +885,8 @@ int launch_umma(const CUtensorMap& tmA, const CUtensorMap& tmB, const Sched& sc,
   return FTK_OK;
 }
 
-// Which CTA grouping to use: 2 (CTA pairs, 256-row tiles) unless FTK_CTA_GROUP=1 is set in the environment.
-int cta_group() {
-  const char* e = getenv("FTK_CTA_GROUP");
-  return (e != nullptr && atoi(e) == 1) ? 1 : 2;
-}
+// Which CTA grouping to use: 2 (CTA pairs, 256-row tiles) unless ftk_set_option(FTK_OPT_CTA_GROUP, 1) was called.
+int cta_group() { return ftk::option(FTK_OPT_CTA_GROUP); }
 
 inline int ceil_div(int64_t a, int64_t b) { return static_cast<int>((a + b - 1) / b); }
 inline int64_t round_up(int64_t a, int64_t b) { return (a + b - 1) / b * b; }
@@ -917,12 +911,10 @@ void plan_chunks(int n_mblk, int n_ntile, int n_groups, int* n_chunks, int* tile
   *n_chunks = ceil_div(n_ntile, *tiles_per_chunk);
 }
 
-// L2 eviction policy per operand role; FTK_HINTS="<a><b><s>" with letters n/f/l overrides (experiments).
+// L2 eviction policy per operand role (a, b, stores): letters n/f/l.  evict_first / evict_last on any role measured
+// no different from normal (profiles/r01_l2hint_experiment.txt), so every kernel passes "nnn".
 uint64_t hint_of(char c) { return c == 'f' ? kEvictFirst : c == 'l' ? kEvictLast : kEvictNormal; }
-void pick_hints(const char* kernel_defaults, int kernel_idx, uint64_t* a, uint64_t* b, uint64_t* s) {
-  // kernel_idx: 0 fwd, 1 dz, 2 dH, 3 dW; FTK_HINTS holds 3 letters per kernel, 12 in all
-  const char* e = getenv("FTK_HINTS");
-  const char* src = (e != nullptr && strlen(e) >= 12) ? e + 3 * kernel_idx : kernel_defaults;
+void pick_hints(const char* src, int, uint64_t* a, uint64_t* b, uint64_t* s) {
   *a = hint_of(src[0]);
   *b = hint_of(src[1]);
   if (s != nullptr) *s = hint_of(src[2]);
@@ -983,7 +975,7 @@ int run_fwd(const void* H, const void* W, const void* bias, const int64_t* targe
   const int n_mblk = ceil_div(M, BM * kCG);
   sc.n_ntile = ceil_div(V, BN);
   int n_chunks;
-  plan_chunks(n_mblk, sc.n_ntile, (sm_count - g_sm_reserve > kCG ? sm_count - g_sm_reserve : kCG) / kCG, &n_chunks,
+  plan_chunks(n_mblk, sc.n_ntile, (sm_count - sm_reserve() > kCG ? sm_count - sm_reserve() : kCG) / kCG, &n_chunks,
               &sc.tiles_per_chunk);
   sc.n_units = n_mblk * n_chunks;
   sc.n_mblk = n_mblk;
@@ -1003,7 +995,7 @@ int run_fwd(const void* H, const void* W, const void* bias, const int64_t* targe
   FTK_CUDA_CHECK(cudaMemsetAsync(ws.ticket, 0, sizeof(unsigned int), st));
   if (int rc = launch_umma<kCG, BN, kStages, false, false, FwdEpi>(tmA, tmB, sc, ep, sm_count, st)) return rc;
   fwd_finalize_kernel<<<ceil_div(M, 256), 256, 0, st>>>(ws.pmax, ws.psum, ws.ztgt, targets, static_cast<int>(M),
-                                                        static_cast<int>(ws.Mpad), n_chunks, lse, ws.blk_loss,
+                                                        static_cast<int>(ws.Mpad), V, n_chunks, lse, ws.blk_loss,
                                                         ws.blk_cnt, ws.ticket, loss_sum, n_valid);
   FTK_CUDA_CHECK(cudaGetLastError());
   return FTK_OK;
@@ -1024,7 +1016,7 @@ int run_fwd_keep(const void* H, const void* W, const void* bias, const int64_t* 
   const int n_mblk = ceil_div(M, BM * kCG);
   sc.n_ntile = ceil_div(V, BN);
   int n_chunks;
-  plan_chunks(n_mblk, sc.n_ntile, (sm_count - g_sm_reserve > kCG ? sm_count - g_sm_reserve : kCG) / kCG, &n_chunks,
+  plan_chunks(n_mblk, sc.n_ntile, (sm_count - sm_reserve() > kCG ? sm_count - sm_reserve() : kCG) / kCG, &n_chunks,
               &sc.tiles_per_chunk);
   sc.n_units = n_mblk * n_chunks;
   sc.n_mblk = n_mblk;
@@ -1047,7 +1039,7 @@ int run_fwd_keep(const void* H, const void* W, const void* bias, const int64_t* 
   FTK_CUDA_CHECK(cudaMemsetAsync(ws.ticket, 0, sizeof(unsigned int), st));
   if (int rc = launch_umma<kCG, BN, kStages, false, false, FwdKeepEpi>(tmA, tmB, sc, ep, sm_count, st)) return rc;
   fwd_finalize_kernel<<<ceil_div(M, 256), 256, 0, st>>>(ws.pmax, ws.psum, ws.ztgt, targets, static_cast<int>(M),
-                                                        static_cast<int>(ws.Mpad), n_chunks, lse, ws.blk_loss,
+                                                        static_cast<int>(ws.Mpad), V, n_chunks, lse, ws.blk_loss,
                                                         ws.blk_cnt, ws.ticket, loss_sum, n_valid);
   FTK_CUDA_CHECK(cudaGetLastError());
   return FTK_OK;
@@ -1188,12 +1180,6 @@ int check_common(const void* H, const void* W, int64_t M, int d, int V, ftk::Dev
 }
 
 }  // namespace
-
-extern "C" int ftk_set_sm_reserve(int32_t n_sms) {
-  FTK_REQUIRE(n_sms >= 0 && n_sms <= 64, "ftk_set_sm_reserve: %d out of range [0, 64]", n_sms);
-  g_sm_reserve = n_sms;
-  return FTK_OK;
-}
 
 extern "C" size_t ftk_lmhead_ce_fwd_workspace(int64_t M, int32_t d, int32_t V) {
   (void)d;

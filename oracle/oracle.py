@@ -233,3 +233,27 @@ def hf_causal_lm_loss_v428(logits: torch.Tensor, labels: torch.Tensor) -> torch.
     shift_logits = logits[..., :-1, :].contiguous()
     shift_labels = labels[..., 1:].contiguous()
     return torch.nn.CrossEntropyLoss()(shift_logits.view(-1, shift_logits.size(-1)), shift_labels.view(-1))
+
+
+# ---------------------------------------------------------------------------------------------- BASELINE configs[0]
+GPTNEO_125M = dict(vocab_size=50257, hidden_size=768, num_layers=12, num_heads=12, max_position_embeddings=2048,
+                   attention_types=[[["global", "local"], 6]], window_size=256)
+
+
+def weight_checksum(w: torch.Tensor) -> np.ndarray:
+    w = w.detach().to("cpu", torch.float64)
+    return np.array([float(w.sum()), float((w * w).sum()), float(w[0].sum()), float(w[-1].sum())])
+
+
+def gptneo125m_lm_head_weight(seed: int = 42) -> torch.Tensor:
+    """lm_head / wte weight [50257, 768] fp32 of the literal GPT-Neo-125M config, random-init under
+    ``torch.manual_seed(seed)`` (the reference's default seed, FT.py:148-154) -- how tests/golden/make_golden.py built
+    the model behind ``config0_gptneo125m.npz``.  The fixture holds a fingerprint instead of the 154 MB matrix."""
+    from transformers import GPTNeoConfig, GPTNeoForCausalLM
+    state = torch.random.get_rng_state()
+    try:
+        torch.manual_seed(seed)
+        model = GPTNeoForCausalLM(GPTNeoConfig(**GPTNEO_125M))
+    finally:
+        torch.random.set_rng_state(state)
+    return model.lm_head.weight.detach().clone()

@@ -24,3 +24,11 @@ def cuda_dev():
     if not torch.cuda.is_available():
         pytest.fail("-m gpu tests need a CUDA device")
     return torch.device("cuda:0")
+
+
+@pytest.fixture
+def cta_group():
+    """Select the single-CTA (1) or CTA-pair (2) tcgen05 kernels for one test; the default (2) is restored after."""
+    from kubernetes_cloud_b200 import _lib
+    yield lambda n: _lib.set_option("cta_group", n)
+    _lib.set_option("cta_group", 2)

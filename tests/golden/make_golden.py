@@ -178,8 +178,74 @@ def make_lmhead():
     run("gptj_tiny", m)
 
 
+NEO125M = dict(vocab_size=50257, hidden_size=768, num_layers=12, num_heads=12, max_position_embeddings=2048,
+               attention_types=[[["global", "local"], 6]], window_size=256)  # GPT-Neo-125M, literal
+
+
+def weight_checksum(w: torch.Tensor) -> np.ndarray:
+    """Fingerprint of a weight matrix rebuilt from its seed on another machine: sum, sum of squares, two rows."""
+    w = w.detach().double()
+    return np.array([float(w.sum()), float((w * w).sum()), float(w[0].sum()), float(w[-1].sum())])
+
+
+def make_config0():
+    """BASELINE.json configs[0]: GPT-Neo-125M (literal config, random init under torch.manual_seed(42), the
+    reference's default seed FT.py:148-154), ctx 2048, batch 1, fp32 on CPU, tokens from the synthetic stream.
+    The model's own loss / gradients at the lm_head boundary, i.e. what ``super().compute_loss`` (FT.py:479) and
+    ``loss.backward()`` produce there.  The 154 MB weight is not stored: tests rebuild it from the same seed and check
+    the fingerprint.  GPT-Neo ties lm_head to wte, so ``wte.weight.grad`` = lm_head part + embedding part; the
+    embedding part is HF's own gradient at the embedding output scattered back to its rows and is subtracted."""
+    from transformers import GPTNeoConfig, GPTNeoForCausalLM
+    sys.path.insert(0, os.path.dirname(os.path.dirname(HERE)))
+    from oracle import oracle as O
+    T = 2048
+    tok = O.synth_tokens(4, T, 50257, 1234, trailing_pads=300)
+    ids_np, _, mask_np, _ = O.gather_numpy(tok, T, [3], 50256, True)  # the padded final context: 300 ignored labels
+    ids = torch.from_numpy(ids_np)
+    mask = torch.from_numpy(mask_np)
+    labels = ids.clone().masked_fill_(~mask, -100)  # FT.py:476-477
+    torch.manual_seed(42)
+    model = GPTNeoForCausalLM(GPTNeoConfig(**NEO125M))
+    model.train()
+    grabbed = {}
+
+    def pre_hook(_m, inp):
+        inp[0].retain_grad()
+        grabbed["h"] = inp[0]
+
+    def emb_hook(_m, _inp, out):
+        out.retain_grad()
+        grabbed["e"] = out
+
+    h1 = model.lm_head.register_forward_pre_hook(pre_hook)
+    h2 = model.transformer.wte.register_forward_hook(emb_hook)
+    out = model(input_ids=ids, attention_mask=mask, labels=labels)
+    out.loss.backward()
+    h1.remove()
+    h2.remove()
+    W = model.lm_head.weight
+    assert W.data_ptr() == model.transformer.wte.weight.data_ptr(), "GPT-Neo ties lm_head to wte"
+    emb_part = torch.zeros_like(W).index_add_(0, ids.reshape(-1), grabbed["e"].grad.reshape(T, -1))
+    d_weight = W.grad - emb_part  # the lm_head's own share
+    h = grabbed["h"].detach().reshape(T, 768)
+    dh = grabbed["h"].grad.reshape(T, 768)
+    rng = np.random.default_rng(5)
+    tgt = labels[0, 1:][labels[0, 1:] >= 0].numpy()
+    w_rows = np.unique(np.concatenate([[0, 50256, 50176, 50200], rng.choice(tgt, 20), rng.integers(0, 50257, 40)]))
+    h_rows = np.unique(np.concatenate([[0, 1, 1747, 1748, 2046, 2047], rng.integers(0, T, 250)]))
+    np.savez_compressed(
+        os.path.join(HERE, "config0_gptneo125m.npz"),
+        hidden=h.numpy(), labels=labels.numpy(), loss=np.float32(out.loss.item()),
+        weight_checksum=weight_checksum(W), seed=np.int64(42),
+        h_rows=h_rows.astype(np.int64), d_hidden_rows=dh[h_rows].numpy(),
+        w_rows=w_rows.astype(np.int64), d_weight_rows=d_weight[w_rows].numpy(), weight_rows=W.detach()[w_rows].numpy(),
+        d_weight_norm=np.float64(d_weight.double().norm()), d_hidden_norm=np.float64(dh.double().norm()))
+    print(f"config0_gptneo125m: loss={out.loss.item():.6f} |dW|={float(d_weight.norm()):.5f} rows={len(w_rows)}")
+
+
 if __name__ == "__main__":
     ns = lift(["TokenizedDataset", "collector", "ModifiedTrainer"])
     make_gather(ns)
     make_order()
     make_lmhead()
+    make_config0()

@@ -40,8 +40,8 @@ SHAPES = [(128, 64, 256, False), (256, 128, 1000, False), (300, 64, 777, True), 
 
 @pytest.mark.parametrize("cg", ["1", "2"])
 @pytest.mark.parametrize("M,d,V,bias", SHAPES)
-def test_forward_backward_parity(cuda_dev, monkeypatch, cg, M, d, V, bias):
-    monkeypatch.setenv("FTK_CTA_GROUP", cg)
+def test_forward_backward_parity(cuda_dev, cta_group, cg, M, d, V, bias):
+    cta_group(int(cg))
     H, W, b, t = mk(M, d, V, bias=bias)
     want = O.lmhead_ce_reference(H, W, b, t)
     loss, n_valid, lse, dH, dW, db = gpu_fwd_bwd(H, W, b, t)
@@ -324,7 +324,7 @@ def test_device_batcher_trainer_sampler_mode(cuda_dev, tmp_path):
         np.testing.assert_array_equal(first["input_ids"].cpu().numpy(), O.gather_numpy(raw, T, want[:3].numpy(), 99, True)[0])
 
 
-def test_random_shapes_both_modes(cuda_dev, monkeypatch):
+def test_random_shapes_both_modes(cuda_dev, cta_group):
     """Randomised small shapes (rows and vocabulary sizes that straddle tile edges, d any multiple of 64), both CTA
     groupings, default (recompute) and keep modes, against the fp32 oracle."""
     from kubernetes_cloud_b200 import ops  # noqa: F401
@@ -334,7 +334,7 @@ def test_random_shapes_both_modes(cuda_dev, monkeypatch):
         d = 64 * int(rng.integers(1, 7))
         V = int(rng.integers(2, 2500))
         bias = bool(rng.integers(0, 2))
-        monkeypatch.setenv("FTK_CTA_GROUP", "1" if case % 3 == 0 else "2")
+        cta_group(1 if case % 3 == 0 else 2)
         H, W, b, t = mk(M, d, V, seed=100 + case, bias=bias, frac_ignore=0.15)
         if (t >= 0).sum() == 0:
             t[0] = 0

@@ -3,12 +3,16 @@
 Hosts such as a plugin inside a runtime that owns all of HBM, or a loop that must not trigger cudaMalloc's
 device-wide synchronisation, have no workspace to pass.  This entry point keeps its scratch in a fixed array inside
 the library image.  The test drives it through the C ABI twice in a row (the second call sees the first call's
-leftovers in the shared scratch) and compares each result with the ordinary, workspace-taking entry point.
+leftovers in the shared scratch) and compares each result with the ordinary, workspace-taking entry point and with
+the fp32 CPU oracle, then once more at the largest size the built-in scratch holds (M = FTK_STATIC_MAX_ROWS, where
+the carve-up fills the array to the byte).
 
 The file name sorts last on purpose: a run that stops at the first failure has then already run every other test.
 """
 import pytest
 import torch
+
+from oracle import oracle as O
 
 pytestmark = pytest.mark.gpu
 LOSS_RTOL, LSE_ATOL = 1e-3, 2e-3  # the tolerances of tests/test_lmhead_gpu.py
@@ -50,6 +54,34 @@ def test_static_scratch_forward_matches_workspace_forward_twice(cuda_dev):
         assert int(n_valid) == int(want_n)
         assert abs(float(loss_sum) - float(want_sum)) <= LOSS_RTOL * abs(float(want_sum))
         assert float((lse - want_lse).abs().max()) <= LSE_ATOL
+        # and against the checker that shares no code with either entry point
+        ref = O.lmhead_ce_reference(H, W, b, t, want_grads=False)
+        assert int(n_valid) == ref["n_valid"]
+        assert abs(float(loss_sum) / int(n_valid) - float(ref["loss"])) <= LOSS_RTOL * abs(float(ref["loss"]))
+        assert float((lse.cpu() - ref["lse"]).abs().max()) <= LSE_ATOL
+
+
+def test_static_scratch_forward_at_its_row_limit(cuda_dev):
+    """M = 16,384 rows is the most the built-in scratch holds: every byte of the array is in use.  Run it twice with
+    different inputs (the second call starts from the first call's leftovers) and check both against the oracle on
+    sampled rows and against the workspace entry point in full."""
+    from kubernetes_cloud_b200 import _lib, ops  # noqa: F401
+    L = _lib.lib()
+    M, d, V = 16384, 256, 50257
+    for seed in (21, 22):
+        H, W, b, t = _inputs(M, d, V, seed, bias=(seed == 22))
+        want_sum, want_n, want_lse = torch.ops.ftk.lmhead_ce_fwd(H, W, b, t)
+        lse = torch.empty(M, dtype=torch.float32, device="cuda")
+        loss_sum = torch.empty(1, dtype=torch.float32, device="cuda")
+        n_valid = torch.empty(1, dtype=torch.int32, device="cuda")
+        _lib.check(_call_static(L, H, W, b, t, lse, loss_sum, n_valid), "ftk_lmhead_ce_fwd_static")
+        torch.cuda.synchronize()
+        assert int(n_valid) == int(want_n) == int((t >= 0).sum())
+        assert abs(float(loss_sum) - float(want_sum)) <= LOSS_RTOL * abs(float(want_sum))
+        assert float((lse - want_lse).abs().max()) <= LSE_ATOL
+        rows = torch.arange(0, M, 61, device="cuda")
+        ref = O.lmhead_ce_reference(H[rows], W, b, t[rows], want_grads=False)
+        assert float((lse[rows].cpu() - ref["lse"]).abs().max()) <= LSE_ATOL
 
 
 def test_static_scratch_forward_rejects_sizes_over_its_limit(cuda_dev):

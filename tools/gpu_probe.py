@@ -136,6 +136,9 @@ STAGES = {
 
 if __name__ == "__main__":
     if len(sys.argv) > 2 and sys.argv[1] == "--run":
+        if os.environ.get("FTK_PROBE_CTA_GROUP"):
+            from kubernetes_cloud_b200 import _lib
+            _lib.set_option("cta_group", int(os.environ["FTK_PROBE_CTA_GROUP"]))
         out = STAGES[sys.argv[2]]()
         print("RESULT " + json.dumps(out))
         sys.exit(0)
@@ -144,7 +147,7 @@ if __name__ == "__main__":
         st, _, cg = nm.partition("@")
         env = dict(os.environ)
         if cg:
-            env["FTK_CTA_GROUP"] = cg
+            env["FTK_PROBE_CTA_GROUP"] = cg  # the child applies it with _lib.set_option("cta_group", ...)
         t0 = time.time()
         try:
             p = subprocess.run([sys.executable, __file__, "--run", st], env=env, capture_output=True, text=True, timeout=240)
