@@ -126,26 +126,17 @@ def set_bwd_slab_rows(rows: int) -> None:
 
 
 def _dw_target(W: torch.Tensor, dw_fp32: bool, dW_into: Optional[torch.Tensor]):
-    """(buffer the dW GEMM writes, dtype code, accumulate flag, tensor to return as dW)."""
+    """(tensor the dW GEMM writes, dtype code, accumulate flag)."""
     if dW_into is None:
         dW = torch.empty(W.shape, dtype=torch.float32 if dw_fp32 else torch.bfloat16, device=W.device)
-        return dW, (_lib.FTK_F32 if dw_fp32 else _lib.FTK_BF16), 0, dW
+        return dW, (_lib.FTK_F32 if dw_fp32 else _lib.FTK_BF16), 0
     _need_cuda(dW_into)
     if dW_into.shape != W.shape or not dW_into.is_contiguous() or dW_into.dtype not in (torch.float32, torch.bfloat16):
         raise _lib.FtkError("dW_into must be a contiguous bf16 or fp32 tensor of the weight's shape")
-    code = _lib.FTK_F32 if dW_into.dtype == torch.float32 else _lib.FTK_BF16
-    return dW_into, code, 1, W.new_empty((0,), dtype=dW_into.dtype)  # an op's output may not alias its input
+    return dW_into, (_lib.FTK_F32 if dW_into.dtype == torch.float32 else _lib.FTK_BF16), 1
 
 
-@torch.library.custom_op("ftk::lmhead_ce_bwd", mutates_args=("dW_into",))
-def lmhead_ce_bwd(H: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor], targets: torch.Tensor,
-                  lse: torch.Tensor, grad_out: Optional[torch.Tensor], n_valid: Optional[torch.Tensor],
-                  grad_scale: float, dw_fp32: bool,
-                  dW_into: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
-    """Returns (dH bf16 [M,d], dW [V,d] bf16 or fp32, dbias fp32 [V] or empty).
-    dZ = (softmax - onehot) * grad_scale * grad_out / n_valid on valid rows.
-    With ``dW_into`` (bf16 or fp32 [V,d]) the dW GEMM adds into that tensor inside its epilogue (tied embeddings,
-    gradient accumulation, an fp32 main gradient) and the returned dW is empty."""
+def _bwd_impl(H, W, bias, targets, lse, grad_out, n_valid, grad_scale, dw_fp32, dW_into):
     global _launches
     _check_hw(H, W, bias, targets)
     _need_cuda(lse, grad_out, n_valid)
@@ -153,7 +144,7 @@ def lmhead_ce_bwd(H: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor]
     V = W.shape[0]
     dev = H.device
     dH = torch.empty((M, d), dtype=torch.bfloat16, device=dev)
-    dW_buf, dw_code, acc, dW = _dw_target(W, dw_fp32, dW_into)
+    dW, dw_code, acc = _dw_target(W, dw_fp32, dW_into)
     dbias = torch.empty((V if bias is not None else 0,), dtype=torch.float32, device=dev)
     if grad_out is not None:
         grad_out = grad_out.to(torch.float32).contiguous()
@@ -162,8 +153,7 @@ def lmhead_ce_bwd(H: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor]
     ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
     with torch.cuda.device(dev):
         rc = L.ftk_lmhead_ce_bwd(H.data_ptr(), W.data_ptr(), _ptr(bias), targets.data_ptr(), lse.data_ptr(), M, d, V,
-                                 grad_scale, _ptr(grad_out), _ptr(n_valid), dH.data_ptr(), dW_buf.data_ptr(),
-                                 dw_code, acc,
+                                 grad_scale, _ptr(grad_out), _ptr(n_valid), dH.data_ptr(), dW.data_ptr(), dw_code, acc,
                                  dbias.data_ptr() if bias is not None else 0, ws.data_ptr(), ws_bytes, _stream(H))
     _lib.check(rc, "ftk_lmhead_ce_bwd")
     slab = _slab_rows if _slab_rows > 0 else 16384
@@ -172,11 +162,34 @@ def lmhead_ce_bwd(H: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor]
     return dH, dW, dbias
 
 
+@torch.library.custom_op("ftk::lmhead_ce_bwd", mutates_args=())
+def lmhead_ce_bwd(H: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor], targets: torch.Tensor,
+                  lse: torch.Tensor, grad_out: Optional[torch.Tensor], n_valid: Optional[torch.Tensor],
+                  grad_scale: float, dw_fp32: bool) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """Returns (dH bf16 [M,d], dW [V,d] bf16 or fp32, dbias fp32 [V] or empty).
+    dZ = (softmax - onehot) * grad_scale * grad_out / n_valid on valid rows."""
+    return _bwd_impl(H, W, bias, targets, lse, grad_out, n_valid, grad_scale, dw_fp32, None)
+
+
 @lmhead_ce_bwd.register_fake
-def _(H, W, bias, targets, lse, grad_out, n_valid, grad_scale, dw_fp32, dW_into=None):
-    dW = (W.new_empty(W.shape, dtype=torch.float32 if dw_fp32 else torch.bfloat16) if dW_into is None
-          else W.new_empty((0,), dtype=dW_into.dtype))
-    return (torch.empty_like(H), dW, H.new_empty((W.shape[0] if bias is not None else 0,), dtype=torch.float32))
+def _(H, W, bias, targets, lse, grad_out, n_valid, grad_scale, dw_fp32):
+    return (torch.empty_like(H), W.new_empty(W.shape, dtype=torch.float32 if dw_fp32 else torch.bfloat16),
+            H.new_empty((W.shape[0] if bias is not None else 0,), dtype=torch.float32))
+
+
+@torch.library.custom_op("ftk::lmhead_ce_bwd_into", mutates_args=("dW_into",))
+def lmhead_ce_bwd_into(H: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor], targets: torch.Tensor,
+                       lse: torch.Tensor, grad_out: Optional[torch.Tensor], n_valid: Optional[torch.Tensor],
+                       grad_scale: float, dW_into: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """The same backward with the dW GEMM adding into ``dW_into`` (bf16 or fp32 [V,d]) inside its epilogue: tied
+    embeddings, gradient accumulation, an fp32 main gradient.  Returns (dH, dbias)."""
+    dH, _, dbias = _bwd_impl(H, W, bias, targets, lse, grad_out, n_valid, grad_scale, False, dW_into)
+    return dH, dbias
+
+
+@lmhead_ce_bwd_into.register_fake
+def _(H, W, bias, targets, lse, grad_out, n_valid, grad_scale, dW_into):
+    return torch.empty_like(H), H.new_empty((W.shape[0] if bias is not None else 0,), dtype=torch.float32)
 
 
 @torch.library.custom_op("ftk::lmhead_ce_fwd_keep", mutates_args=())
@@ -215,13 +228,7 @@ def _(H, W, bias, targets):
             H.new_empty(((V + 255) // 256 * ((M + 255) // 256 * 256),), dtype=torch.float32))
 
 
-@torch.library.custom_op("ftk::lmhead_ce_bwd_kept", mutates_args=("probs", "dW_into"))
-def lmhead_ce_bwd_kept(H: torch.Tensor, W: torch.Tensor, has_bias: bool, targets: torch.Tensor, lse: torch.Tensor,
-                       probs: torch.Tensor, cref: torch.Tensor, grad_out: Optional[torch.Tensor],
-                       n_valid: Optional[torch.Tensor], grad_scale: float, dw_fp32: bool,
-                       dW_into: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
-    """Backward from kept numerators (no logit recompute).  ``probs`` is overwritten with dZ.  ``dW_into`` as in
-    ``lmhead_ce_bwd``."""
+def _bwd_kept_impl(H, W, has_bias, targets, lse, probs, cref, grad_out, n_valid, grad_scale, dw_fp32, dW_into):
     global _launches
     _check_hw(H, W, None, targets)
     _need_cuda(lse, probs, cref, grad_out, n_valid)
@@ -229,25 +236,49 @@ def lmhead_ce_bwd_kept(H: torch.Tensor, W: torch.Tensor, has_bias: bool, targets
     V = W.shape[0]
     dev = H.device
     dH = torch.empty((M, d), dtype=torch.bfloat16, device=dev)
-    dW_buf, dw_code, acc, dW = _dw_target(W, dw_fp32, dW_into)
+    dW, dw_code, acc = _dw_target(W, dw_fp32, dW_into)
     dbias = torch.empty((V if has_bias else 0,), dtype=torch.float32, device=dev)
     if grad_out is not None:
         grad_out = grad_out.to(torch.float32).contiguous()
     with torch.cuda.device(dev):
         rc = _lib.lib().ftk_lmhead_ce_bwd_kept(H.data_ptr(), W.data_ptr(), targets.data_ptr(), lse.data_ptr(),
                                                probs.data_ptr(), cref.data_ptr(), M, d, V, grad_scale, _ptr(grad_out),
-                                               _ptr(n_valid), dH.data_ptr(), dW_buf.data_ptr(), dw_code, acc,
+                                               _ptr(n_valid), dH.data_ptr(), dW.data_ptr(), dw_code, acc,
                                                dbias.data_ptr() if has_bias else 0, _stream(H))
     _lib.check(rc, "ftk_lmhead_ce_bwd_kept")
     _launches += 3 + (1 if has_bias else 0)
     return dH, dW, dbias
 
 
+@torch.library.custom_op("ftk::lmhead_ce_bwd_kept", mutates_args=("probs",))
+def lmhead_ce_bwd_kept(H: torch.Tensor, W: torch.Tensor, has_bias: bool, targets: torch.Tensor, lse: torch.Tensor,
+                       probs: torch.Tensor, cref: torch.Tensor, grad_out: Optional[torch.Tensor],
+                       n_valid: Optional[torch.Tensor], grad_scale: float, dw_fp32: bool
+                       ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """Backward from kept numerators (no logit recompute).  ``probs`` is overwritten with dZ."""
+    return _bwd_kept_impl(H, W, has_bias, targets, lse, probs, cref, grad_out, n_valid, grad_scale, dw_fp32, None)
+
+
 @lmhead_ce_bwd_kept.register_fake
-def _(H, W, has_bias, targets, lse, probs, cref, grad_out, n_valid, grad_scale, dw_fp32, dW_into=None):
-    dW = (W.new_empty(W.shape, dtype=torch.float32 if dw_fp32 else torch.bfloat16) if dW_into is None
-          else W.new_empty((0,), dtype=dW_into.dtype))
-    return (torch.empty_like(H), dW, H.new_empty((W.shape[0] if has_bias else 0,), dtype=torch.float32))
+def _(H, W, has_bias, targets, lse, probs, cref, grad_out, n_valid, grad_scale, dw_fp32):
+    return (torch.empty_like(H), W.new_empty(W.shape, dtype=torch.float32 if dw_fp32 else torch.bfloat16),
+            H.new_empty((W.shape[0] if has_bias else 0,), dtype=torch.float32))
+
+
+@torch.library.custom_op("ftk::lmhead_ce_bwd_kept_into", mutates_args=("probs", "dW_into"))
+def lmhead_ce_bwd_kept_into(H: torch.Tensor, W: torch.Tensor, has_bias: bool, targets: torch.Tensor,
+                            lse: torch.Tensor, probs: torch.Tensor, cref: torch.Tensor,
+                            grad_out: Optional[torch.Tensor], n_valid: Optional[torch.Tensor], grad_scale: float,
+                            dW_into: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``lmhead_ce_bwd_kept`` with the dW GEMM adding into ``dW_into``.  Returns (dH, dbias)."""
+    dH, _, dbias = _bwd_kept_impl(H, W, has_bias, targets, lse, probs, cref, grad_out, n_valid, grad_scale, False,
+                                  dW_into)
+    return dH, dbias
+
+
+@lmhead_ce_bwd_kept_into.register_fake
+def _(H, W, has_bias, targets, lse, probs, cref, grad_out, n_valid, grad_scale, dW_into):
+    return torch.empty_like(H), H.new_empty((W.shape[0] if has_bias else 0,), dtype=torch.float32)
 
 
 _backward_mode = "recompute"
@@ -305,19 +336,27 @@ class _FusedLmHeadCE(torch.autograd.Function):
     def backward(ctx, grad_out):
         weight = ctx.saved_tensors[1]
         into = _wgrad_target(weight) if ctx.needs_input_grad[1] else None
+        go = grad_out.reshape(1)
+        dW = None
         if ctx.keep:
             if ctx.consumed:
                 raise _lib.FtkError("the kept softmax numerators were consumed by the first backward "
                                     "(use set_backward_mode('recompute') to backpropagate twice)")
             hidden, weight, bias, targets, lse, n_valid, probs, cref = ctx.saved_tensors
-            dH, dW, dbias = torch.ops.ftk.lmhead_ce_bwd_kept(hidden, weight, bias is not None, targets, lse, probs, cref,
-                                                             grad_out.reshape(1), n_valid, 1.0, False, into)
+            if into is not None:
+                dH, dbias = torch.ops.ftk.lmhead_ce_bwd_kept_into(hidden, weight, bias is not None, targets, lse, probs,
+                                                                  cref, go, n_valid, 1.0, into)
+            else:
+                dH, dW, dbias = torch.ops.ftk.lmhead_ce_bwd_kept(hidden, weight, bias is not None, targets, lse, probs,
+                                                                 cref, go, n_valid, 1.0, False)
             ctx.consumed = True
         else:
             hidden, weight, bias, targets, lse, n_valid = ctx.saved_tensors
-            dH, dW, dbias = torch.ops.ftk.lmhead_ce_bwd(hidden, weight, bias, targets, lse, grad_out.reshape(1),
-                                                        n_valid, 1.0, False, into)
-        return dH, (None if into is not None else dW), (dbias.to(bias.dtype) if bias is not None else None), None
+            if into is not None:
+                dH, dbias = torch.ops.ftk.lmhead_ce_bwd_into(hidden, weight, bias, targets, lse, go, n_valid, 1.0, into)
+            else:
+                dH, dW, dbias = torch.ops.ftk.lmhead_ce_bwd(hidden, weight, bias, targets, lse, go, n_valid, 1.0, False)
+        return dH, dW, (dbias.to(bias.dtype) if bias is not None else None), None
 
 
 def fused_lmhead_ce(hidden: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor],
