@@ -7,15 +7,21 @@ and backward -> data-parallel all-reduce of the lm_head / embedding gradient.
 
 Workload (BASELINE.json configs[2], the one the metric is quoted on): GPT-Neo-1.3B head, d = 2048, V = 50257,
 context 2048, 8 contexts per GPU per step = 16,384 tokens.  One "step" = one pass of the hot path over one batch:
-gather 8 windows from the HBM-resident uint16 token stream (ids, shifted+masked labels, mask), loss = fused
-lm_head+CE(hidden, W, targets), backward -> dH, dW, all-reduce(dW)/N on the communication stream.  The transformer
-trunk is out of scope for this tier: the hidden states are synthetic bf16, resident in HBM.
+gather 8 windows from the HBM-resident uint16 token stream (ids, shifted+masked labels, mask); fused lm_head+CE
+forward AND backward in one call (loss, dH, dW added into W's fp32 main gradient); all-reduce(dW)/N through GradSync,
+started by the dW-done event while the last dH GEMM still runs; gradient-norm clip + fused AdamW on W (FusedAdamW).
+The reduced gradient is applied before the next forward reads W, as in a real training step.  The transformer trunk
+is out of scope for this tier: the hidden states are synthetic bf16, resident in HBM.
 Inputs (W 206 MB + H 67 MB) exceed the 126 MB L2, so no explicit flush is needed between steps.
 
 One JSON line on stdout (rank 0).  ``value`` = tokens/s over all GPUs with inputs resident in HBM; ``e2e`` = the same
 with this step's token windows and hidden states copied from pinned host memory and the loss read back, inside the
-timed region; ``roofline`` = the fused forward kernel against the measured bf16 peak; ``cpu_baseline`` = the oracle's
-CPU restatement of the same path on a bounded sample.
+timed region; ``roofline`` = the step's dominant tensor kernel against the measured bf16 peak, its duration taken
+from the library's launch timeline (CUDA events around every launch inside the timed steps); ``cpu_baseline`` = the
+oracle's CPU restatement of the same path on a bounded sample.  At N > 1 the line also carries
+``allreduce_max_rel_err`` (reduced dW against an independently gathered mean; the run fails above tolerance),
+``exposed_comm_ms_per_step`` and ``full_gradient_allreduce`` (the whole gradient set of GPT-Neo-1.3B and GPT-J-6B
+in 128 MB buckets through the same communicator).
 """
 from __future__ import annotations
 
@@ -36,6 +42,11 @@ D_MODEL, VOCAB, CTX, BATCH = 2048, 50257, 2048, 8  # GPT-Neo-1.3B head (GPTNeoCo
 N_CTX_FILE = 4096                                   # contexts in the synthetic token stream
 PAD_ID = 50256
 WORKLOAD = "GPT-Neo-1.3B lm_head+CE hot path: d=2048 V=50257 ctx=2048 batch=8/GPU (16384 tokens/GPU/step), bf16"
+
+
+def bench_config(n_gpus: int) -> dict:
+    """The ``config`` object both arms print (identical for the same N, so the driver can match the two lines)."""
+    return {"workload": WORKLOAD, "tokens_per_gpu_per_step": BATCH * CTX, "parallelism": f"dp{n_gpus}"}
 
 
 def measured_peaks():
@@ -173,7 +184,8 @@ def main_reference(args) -> None:
     line = {"impl": "reference", "metric": "tokens/s", "value": val, "unit": "tokens/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "step_sample": "1 context (2048 tokens) per step on the host cores"},
+            "config": bench_config(args.gpus),
+            "config_notes": {"step_sample": "each CPU step is 1 context (2048 tokens) of the workload on the host cores"},
             "cpu_baseline": {"value": val, "unit": "tokens/s", "cores": torch.get_num_threads(), "kind": "port",
                              "sample": f"{args.steps} steps of 1 context (2048 tokens)", "host_cpus": os.cpu_count()},
             "e2e": {"value": val, "unit": "tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -183,90 +195,44 @@ def main_reference(args) -> None:
 
 # ------------------------------------------------------------------------------------------------ GPU arm
 def main_gpu(args) -> None:
+    import ctypes
     import numpy as np
     import torch
     import torch.distributed as dist
     from kubernetes_cloud_b200 import _lib, ops
+    from kubernetes_cloud_b200.dp import GradSync
+    from kubernetes_cloud_b200.optim import FusedAdamW
     from kubernetes_cloud_b200.ordering import epoch_batches
-    import ctypes
+    from kubernetes_cloud_b200.tokenfile import synthetic_token_stream
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    sm_reserve = int(os.environ.get("FTK_BENCH_SM_RESERVE", "8" if world <= 2 else "16")) if world > 1 else 0
+    # SMs the last slab's dH GEMM leaves to the all-reduce of dW that runs beside it
+    sm_reserve = int(os.environ.get("FTK_BENCH_SM_RESERVE", "16")) if world > 1 else 0
+    wire = os.environ.get("FTK_BENCH_WIRE", "fp32")  # fp32: the reference's communication_data_type; bf16: half the bytes
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         if sm_reserve:
             os.environ.setdefault("NCCL_MAX_CTAS", str(sm_reserve))  # the all-reduce must fit the reserved SMs
         dist.init_process_group("nccl", device_id=dev)
     L = _lib.lib()
+    stream = torch.cuda.current_stream(dev)
 
     # ---- synthetic inputs, resident in HBM (and a pinned host copy for the e2e leg)
-    from kubernetes_cloud_b200.tokenfile import synthetic_token_stream
     tok_host = torch.from_numpy(synthetic_token_stream(N_CTX_FILE, CTX, VOCAB, 7, pad_id=PAD_ID).view(np.int16)).pin_memory()
     tokens = tok_host.to(dev)
     g = torch.Generator(device=dev).manual_seed(42 + rank)
     gw = torch.Generator(device=dev).manual_seed(20240607)  # not the H seed: equal streams make H rows = W rows
-    W = (torch.randn(VOCAB, D_MODEL, device=dev, generator=gw) * 0.02).to(torch.bfloat16)
+    W = torch.nn.Parameter((torch.randn(VOCAB, D_MODEL, device=dev, generator=gw) * 0.02).to(torch.bfloat16))
     M = BATCH * CTX
     H = torch.randn(M, D_MODEL, device=dev, generator=g).to(torch.bfloat16)
     H_host = [H.cpu().pin_memory(), H.cpu().pin_memory()]
     batches = list(epoch_batches(N_CTX_FILE, BATCH, seed=42, shuffle=True, rank=rank, world=world))
     idx_dev = [b.to(dev) for b in batches]
-
-    # ---- DP communicator (ftk_dp_* over NCCL) for the gradient all-reduce
-    handle = None
-    if world > 1:
-        buf = ctypes.create_string_buffer(128)
-        box = [None]
-        if rank == 0:
-            _lib.check(L.ftk_dp_unique_id(buf), "ftk_dp_unique_id")
-            box = [bytes(buf.raw)]
-        dist.broadcast_object_list(box, src=0)
-        buf = ctypes.create_string_buffer(box[0], 128)
-        handle = ctypes.c_void_p()
-        _lib.check(L.ftk_dp_init(buf, rank, world, ctypes.byref(handle)), "ftk_dp_init")
-
-    stream = torch.cuda.current_stream(dev)
-    ev_f0, ev_f1, ev_b1 = [], [], []
-    state = {"dW": None}
-    comm_launches = [0]
-
-    def hot_path(i: int, hidden: torch.Tensor, tok: torch.Tensor, idx: torch.Tensor, timed: bool, keep: bool = False):
-        ids, targets, mask, n_valid_rows = torch.ops.ftk.gather_windows(tok, idx, CTX, PAD_ID, True, True)
-        if timed:
-            e0 = torch.cuda.Event(enable_timing=True); e0.record(stream); ev_f0.append(e0)
-        if sm_reserve and state["dW"] is not None:
-            L.ftk_set_sm_reserve(sm_reserve)  # the previous step's all-reduce runs beside this forward
-        if keep:
-            loss_sum, n_valid, lse, probs, cref = torch.ops.ftk.lmhead_ce_fwd_keep(hidden, W, None, targets.view(-1))
-        else:
-            loss_sum, n_valid, lse = torch.ops.ftk.lmhead_ce_fwd(hidden, W, None, targets.view(-1))
-        if sm_reserve:
-            L.ftk_set_sm_reserve(0)
-        if timed:
-            e1 = torch.cuda.Event(enable_timing=True); e1.record(stream); ev_f1.append(e1)
-        if handle is not None and state["dW"] is not None:
-            _lib.check(L.ftk_dp_join(handle, stream.cuda_stream), "ftk_dp_join")  # previous dW reduce must be done
-        if keep:
-            dH, dW, _ = torch.ops.ftk.lmhead_ce_bwd_kept(hidden, W, False, targets.view(-1), lse, probs, cref, None,
-                                                         n_valid, 1.0, False)
-        else:
-            dH, dW, _ = torch.ops.ftk.lmhead_ce_bwd(hidden, W, None, targets.view(-1), lse, None, n_valid, 1.0, False)
-        if timed:
-            e2 = torch.cuda.Event(enable_timing=True); e2.record(stream); ev_b1.append(e2)
-        state["dW"] = dW
-        if handle is not None:  # averaged gradient, on the comm stream, overlapping the next step's gather + forward
-            _lib.check(L.ftk_dp_allreduce(handle, dW.data_ptr(), dW.numel(), _lib.FTK_BF16, 1.0 / world,
-                                          stream.cuda_stream), "ftk_dp_allreduce")
-            # the scale is folded into the NCCL op: no kernel of ours on the comm stream
-        return loss_sum, n_valid
-
-    def finish_comm():
-        if handle is not None:
-            _lib.check(L.ftk_dp_join(handle, stream.cuda_stream), "ftk_dp_join")
+    nb = len(idx_dev)
 
     def barrier():
         torch.cuda.synchronize(dev)
@@ -281,13 +247,23 @@ def main_gpu(args) -> None:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t)
 
+    def timed_loop(fn, n: int) -> float:
+        """Device time of n calls of fn(i), bracketed by barrier + synchronize on both sides, max over ranks (ms)."""
+        barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record(stream)
+        for i in range(n):
+            fn(i)
+        b.record(stream)
+        barrier()
+        return max_over_ranks(a.elapsed_time(b))
+
     # ================= bulk gather bandwidth (HBM roofline of G1; outside the step: one step's gather is 0.3 MB).
     # Measured first, on a GPU that is not yet power-capped by the GEMM phase: the kernel tracks the SM/L2 clock. ====
     n_bulk = 4096 * 8  # 2^26 tokens per launch, each context of a 134 MB source read exactly once (a permutation):
     # the source is larger than the 126 MB L2, so the 2 B/token read side is HBM traffic as well
     big_tokens = torch.randint(0, VOCAB, (n_bulk * CTX,), device=dev, dtype=torch.int32).to(torch.int16)
     big_idx = torch.randperm(n_bulk, device=dev)
-
     # The kernel is timed through the C ABI into preallocated outputs: going through the torch op would add four
     # fresh 0.1-0.5 GB allocations per call to the measurement (that path measured 4.3-4.7 TB/s for the same kernel).
     b_ids = torch.empty(n_bulk, CTX, dtype=torch.int64, device=dev)
@@ -314,90 +290,149 @@ def main_gpu(args) -> None:
         return 19.0 * n_bulk * CTX / (g0.elapsed_time(g1) / 10 / 1e3) / 1e9
 
     gather_gbs = bulk_gather_gbs()
-    _lib.set_option("gather_variant", 1)
-    gather_direct_gbs = bulk_gather_gbs()
+    _lib.set_option("gather_variant", 1 - int(os.environ.get("FTK_BENCH_GATHER_DEFAULT_DIRECT", "0")))
+    gather_other_gbs = bulk_gather_gbs()
     _lib.set_option("gather_variant", 0)
     _lib.set_option("gather_stores", 2)
     gather_plain_gbs = bulk_gather_gbs()
     _lib.set_option("gather_stores", 0)
     del b_ids, b_lab, b_msk, b_nv, big_tokens
 
-    # ================= optimizer step on the lm_head / wte bucket (HBM roofline) =================
-    n_par = VOCAB * D_MODEL
-    p_bf = W.clone()
-    g_bf = torch.randn(n_par, device=dev, dtype=torch.float32).mul_(1e-3).to(torch.bfloat16)
-    master = p_bf.float().view(-1)
-    m_buf = torch.zeros(n_par, device=dev)
-    v_buf = torch.zeros(n_par, device=dev)
-    sq = torch.zeros(1, device=dev)
-    coef = torch.ones(1, device=dev)
-    ws_n = torch.empty(L.ftk_grad_sqnorm_workspace(), dtype=torch.uint8, device=dev)
+    # ================= the step: gather -> fused lm_head+CE forward+backward -> all-reduce(dW) -> clip + AdamW(W) =====
+    # GradSync owns W's gradient bucket (fp32 main gradient unless FTK_BENCH_WIRE=bf16) and the NCCL communicator;
+    # FusedAdamW owns W's fp32 master copy and moments.  The dependency of a real training step is honoured: the
+    # reduced gradient is applied to W before W is read by the next forward.
+    sync = GradSync([W], rank, world, main_grads=(wire == "fp32"))
+    opt = FusedAdamW(sync, lr=5e-5, weight_decay=0.01, max_grad_norm=1.0)
+    dw_event = None
+    if world > 1:
+        dw_event = torch.cuda.Event()
+        dw_event.record(stream)
+        ops.set_dw_done_event(dw_event)
+        _lib.set_option("sm_reserve", sm_reserve)
 
-    def adam_once(step_no: int):
-        _lib.check(L.ftk_grad_sqnorm(g_bf.data_ptr(), n_par, _lib.FTK_BF16, sq.data_ptr(), 0, ws_n.data_ptr(),
-                                     ws_n.numel(), stream.cuda_stream), "ftk_grad_sqnorm")
-        _lib.check(L.ftk_clip_coef(sq.data_ptr(), 1.0, coef.data_ptr(), stream.cuda_stream), "ftk_clip_coef")
-        _lib.check(L.ftk_adamw_step(p_bf.data_ptr(), g_bf.data_ptr(), master.data_ptr(), m_buf.data_ptr(),
-                                    v_buf.data_ptr(), n_par, _lib.FTK_BF16, _lib.FTK_BF16, 5e-5, 0.9, 0.999, 1e-8, 0.01,
-                                    step_no, 1.0, coef.data_ptr(), stream.cuda_stream), "ftk_adamw_step")
+    fused_mode = [True]
 
-    for i in range(10):
-        adam_once(i + 1)
-    torch.cuda.synchronize(dev)
-    a0 = torch.cuda.Event(enable_timing=True)
-    a1 = torch.cuda.Event(enable_timing=True)
-    a0.record(stream)
-    for i in range(10):
-        adam_once(i + 11)
-    a1.record(stream)
-    torch.cuda.synchronize(dev)
-    adam_ms = a0.elapsed_time(a1) / 10
-    adam_gbs = (28.0 + 2.0) * n_par / (adam_ms / 1e3) / 1e9  # 28 B/param AdamW + 2 B/param gradient-norm read
-    del p_bf, g_bf, master, m_buf, v_buf
+    def step(hidden: torch.Tensor, tok: torch.Tensor, idx: torch.Tensor, comm: bool = True, optimizer: bool = True):
+        ids, targets, mask, n_valid_rows = torch.ops.ftk.gather_windows(tok, idx, CTX, PAD_ID, True, True)
+        sync.zero_grad()
+        h = hidden.detach().requires_grad_(True)
+        loss = ops.fused_lmhead_ce(h, W, None, targets.view(-1))  # dH, dW (into W's gradient bucket) made here
+        early = fused_mode[0] and world > 1 and comm
+        if early:
+            sync.mark_ready(W, dw_event)  # all-reduce(dW) starts when dW is done, beside the last slab's dH GEMM
+        loss.backward()                   # hands dH to h.grad (upstream gradient 1: nothing to rescale)
+        if world > 1 and comm and not early:
+            sync.mark_ready(W)            # recompute mode: dW only exists after backward
+        sync.finish(reduce=comm)
+        if optimizer:
+            opt.step()
+        return loss.detach(), h.grad
 
-    nb = len(idx_dev)
-    # ================= device-resident leg (value) =================
+    def run_steps(n: int, base: int, **kw):
+        out = None
+        for i in range(n):
+            out = step(H, tokens, idx_dev[(base + i) % nb], **kw)
+        return out
+
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    for i in range(args.warmup):
-        hot_path(i, H, tokens, idx_dev[i % nb], False)
-    finish_comm()
+    run_steps(args.warmup, 0)
     barrier()
     l0 = ops.launch_count()
+    _lib.timeline_enable(True)
     sampler.mark_begin()
-    t_begin = torch.cuda.Event(enable_timing=True)
-    t_end = torch.cuda.Event(enable_timing=True)
+    t_begin, t_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t_begin.record(stream)
-    for i in range(args.steps):
-        loss_sum, n_valid = hot_path(args.warmup + i, H, tokens, idx_dev[(args.warmup + i) % nb], True)
-    finish_comm()
+    loss, _ = run_steps(args.steps, args.warmup)
     t_end.record(stream)
     barrier()
     sampler.mark_end()
     clocks = sampler.stop() if rank == 0 else None
-    launches = ops.launch_count() - l0 + comm_launches[0]
+    timeline = _lib.timeline_read()
+    _lib.timeline_enable(False)
+    # ours: gather + fused call + rescale checks (counted in ops) + grad-norm, clip, AdamW per step
+    launches = ops.launch_count() - l0 + 3 * args.steps
     ms_total = max_over_ranks(t_begin.elapsed_time(t_end))
     ms_step = ms_total / args.steps
     value = world * M * args.steps / (ms_total / 1e3)
-    fwd_ms = sum(a.elapsed_time(b) for a, b in zip(ev_f0, ev_f1)) / args.steps
-    bwd_ms = sum(a.elapsed_time(b) for a, b in zip(ev_f1, ev_b1)) / args.steps
-    loss_val = float(loss_sum) / max(int(n_valid), 1)
+    loss_val = float(loss)
+    per_kernel = {}
+    for name, ms in timeline:
+        e = per_kernel.setdefault(name, [0, 0.0])
+        e[0] += 1
+        e[1] += ms
+    kern = {k: {"launches_per_step": v[0] / args.steps, "ms_per_step": v[1] / args.steps} for k, v in per_kernel.items()}
 
-    # ================= the same leg in the opt-in keep-numerators mode (not the headline) ==========
-    for i in range(args.warmup):
-        hot_path(i, H, tokens, idx_dev[i % nb], False, keep=True)
-    finish_comm()
-    barrier()
-    k0 = torch.cuda.Event(enable_timing=True)
-    k1 = torch.cuda.Event(enable_timing=True)
-    k0.record(stream)
-    for i in range(args.steps):
-        hot_path(args.warmup + i, H, tokens, idx_dev[(args.warmup + i) % nb], False, keep=True)
-    finish_comm()
-    k1.record(stream)
-    barrier()
-    keep_ms = max_over_ranks(k0.elapsed_time(k1)) / args.steps
+    # ---- the same step without its parts, to price them (short loops)
+    n_short = max(5, args.steps // 2)
+    exposed_comm_ms = None
+    if world > 1:
+        run_steps(2, 0, comm=False)
+        ms_nocomm = timed_loop(lambda i: step(H, tokens, idx_dev[i % nb], comm=False), n_short) / n_short
+        run_steps(2, 0)
+        ms_comm = timed_loop(lambda i: step(H, tokens, idx_dev[i % nb]), n_short) / n_short
+        exposed_comm_ms = ms_comm - ms_nocomm
+    run_steps(2, 0, optimizer=False)
+    ms_noopt = timed_loop(lambda i: step(H, tokens, idx_dev[i % nb], optimizer=False), n_short) / n_short
+
+    # ---- the r01 default for comparison: separate forward, backward that recomputes the logits
+    ops.set_backward_mode("recompute")
+    fused_mode[0] = False
+    run_steps(2, 0)
+    recompute_ms = timed_loop(lambda i: step(H, tokens, idx_dev[i % nb]), n_short) / n_short
+    ops.set_backward_mode("fused")
+    fused_mode[0] = True
+
+    # ================= multi-GPU correctness, visible to the driver: the reduced dW against an independent mean =========
+    allreduce_err = None
+    if world > 1:
+        sync.zero_grad()
+        h = H.detach().requires_grad_(True)
+        ids, targets, _, _ = torch.ops.ftk.gather_windows(tokens, idx_dev[0], CTX, PAD_ID, True, True)
+        with sync.no_sync():
+            ops.fused_lmhead_ce(h, W, None, targets.view(-1)).backward()  # local gradient only
+        flat = sync.buckets[0].flat
+        sample_idx = torch.arange(0, flat.numel(), max(1, flat.numel() // (1 << 20)), device=dev)[: 1 << 20]
+        mine = flat[sample_idx].float().clone()
+        gathered = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(gathered, mine)  # second, independent route: torch.distributed all_gather + local fp64 mean
+        want = torch.stack(gathered).double().mean(0)
+        sync.mark_ready(W)
+        sync.finish()
+        torch.cuda.synchronize(dev)
+        got = flat[sample_idx].double()
+        err = float((got - want).norm() / want.norm().clamp_min(1e-30))
+        t = torch.tensor([err], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        allreduce_err = float(t)
+
+    # ================= whole gradient set through the same communicator =========================
+    full_grad = None
+    if world > 1:
+        full_grad = {}
+        handle = sync._handle
+        for name, n_el in (("gpt-neo-1.3b", 1_315_575_808), ("gpt-j-6b", 6_050_882_784)):
+            for dt, code, esz in ((torch.float32, _lib.FTK_F32, 4), (torch.bfloat16, _lib.FTK_BF16, 2)):
+                bucket_el = (128 << 20) // esz
+                flat = torch.zeros(n_el + (-n_el) % 8, dtype=dt, device=dev)
+                offs = list(range(0, flat.numel(), bucket_el))
+
+                def reduce_all():
+                    for o in offs:
+                        n = min(bucket_el, flat.numel() - o)
+                        _lib.check(L.ftk_dp_allreduce(handle, flat.data_ptr() + o * esz, n, code, 1.0 / world,
+                                                      stream.cuda_stream), "ftk_dp_allreduce")
+                    _lib.check(L.ftk_dp_join(handle, stream.cuda_stream), "ftk_dp_join")
+
+                reduce_all()
+                ms = timed_loop(lambda i: reduce_all(), 2) / 2
+                bus = 2.0 * (world - 1) / world * flat.numel() * esz / (ms / 1e3) / 1e9
+                full_grad[f"{name}_{'fp32' if esz == 4 else 'bf16'}"] = {
+                    "elements": n_el, "buckets": len(offs), "bucket_mb": 128, "ms": ms, "bus_gbs": bus}
+                del flat
+        _lib.set_option("sm_reserve", sm_reserve)
 
     # ================= end-to-end leg: host buffers in, loss out, copies inside the timed region =================
     copy_stream = torch.cuda.Stream(dev)
@@ -409,7 +444,6 @@ def main_gpu(args) -> None:
     tok_rows = tok_host.view(N_CTX_FILE, CTX)
     host_batch = [torch.empty(BATCH, CTX, dtype=torch.int16).pin_memory() for _ in range(2)]
     loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
-    nval_host = torch.empty(1, dtype=torch.int32).pin_memory()
 
     def upload(i: int):
         s = i & 1
@@ -428,18 +462,15 @@ def main_gpu(args) -> None:
             if i + 1 < base + n:
                 upload(i + 1)  # next step's H2D overlaps this step's compute
             stream.wait_event(ev_copied[s])
-            ls, nv = hot_path(i, stage_h[s], stage_tok[s], idx_local, False)
+            ls, _ = step(stage_h[s], stage_tok[s], idx_local)
             ev_consumed[s].record(stream)
-            loss_host.copy_(ls, non_blocking=True)
-            nval_host.copy_(nv, non_blocking=True)
-        finish_comm()
+            loss_host.copy_(ls.reshape(1), non_blocking=True)
 
-    for s in range(2):
-        ev_consumed[s].record(stream)
+    for s_ in range(2):
+        ev_consumed[s_].record(stream)
     e2e_steps(max(args.warmup, 2), 0)
     barrier()
-    t0 = torch.cuda.Event(enable_timing=True)
-    t1 = torch.cuda.Event(enable_timing=True)
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0.record(stream)
     e2e_steps(args.steps, 1000)
     t1.record(stream)
@@ -447,72 +478,99 @@ def main_gpu(args) -> None:
     e2e_ms = max_over_ranks(t0.elapsed_time(t1))
     e2e_value = world * M * args.steps / (e2e_ms / 1e3)
     h2d = BATCH * CTX * 2 + M * D_MODEL * 2
-    d2h = 8
+    d2h = 4
 
-    if handle is not None:
-        L.ftk_dp_destroy(handle)
+    ops.set_dw_done_event(None)
+    sync.close()
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
     peaks = measured_peaks()
-    flops_fwd = 2.0 * M * VOCAB * D_MODEL
-    ach_fwd = flops_fwd / (fwd_ms / 1e3) / 1e12
+    flops_gemm = 2.0 * M * VOCAB * D_MODEL  # one [tokens x vocab x d] contraction: forward, dH and dW are one each
+    tf = lambda ms: flops_gemm / (ms / 1e3) / 1e12  # noqa: E731
+    tensor_ms = {k: kern[k]["ms_per_step"] for k in ("fwd_keep", "dH", "dW") if k in kern}
+    dom = max(tensor_ms, key=tensor_ms.get)
+    dom_desc = {"fwd_keep": "umma_kernel<FwdKeepEpi> (lm_head GEMM + online-softmax CE + bf16 numerators)",
+                "dH": "umma_kernel<StoreEpi> dH = dZ.W", "dW": "umma_kernel<StoreEpi> dW += dZ^T.H"}[dom]
     traffic = None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
-        traffic = json.load(open(tp)).get("fwd_dram_bytes_per_launch")
+        traffic = json.load(open(tp)).get(f"{dom}_dram_bytes_per_step")
+    fused_ms = sum(tensor_ms.values()) + kern.get("convert", {}).get("ms_per_step", 0.0)
+    conv = kern.get("convert")
     line = {
         "metric": "tokens/s", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "tokens_per_gpu_per_step": M, "parallelism": f"dp{world}",
+        "config": bench_config(world),
+        "config_notes": {
+                   "step": "gather 8 windows -> fused lm_head+CE forward+backward in one call (dH, dW) -> "
+                           "all-reduce(dW)/N -> grad-norm clip + AdamW on W; W is updated before the next forward",
                    "l2": "inputs (W 206 MB + H 67 MB) larger than the 126 MB L2; no explicit flush",
-                   "grad_sync": (f"ncclAllReduce(avg) of dW (103M bf16) on the comm stream, running beside the next step's "
-                                 f"forward, which leaves {sm_reserve} SMs to NCCL (NCCL_MAX_CTAS={sm_reserve})")
+                   "grad_sync": (f"GradSync: ncclAllReduce(avg) of dW (103M {wire}) on the comm stream, started by the "
+                                 f"dW-done event and running beside the last slab's dH GEMM, which leaves {sm_reserve} "
+                                 f"SMs to NCCL (NCCL_MAX_CTAS={sm_reserve}); the optimizer waits for it")
                    if world > 1 else "none (1 GPU)"},
         "tokens_per_s_per_gpu": value / world,
         "loss": loss_val,
-        "roofline": {"bound": "tensor", "kernel": "umma_kernel<FwdEpi> (fused lm_head GEMM + online-softmax CE)",
-                     "achieved": ach_fwd, "peak": peaks["sustained"], "unit": "TFLOP/s", "frac": ach_fwd / peaks["sustained"],
-                     "traffic": traffic, "peak_source": f"{peaks['src']} sustained bf16 (kernel timed inside a long step)",
-                     "frac_of_burst": ach_fwd / peaks["burst"], "frac_of_nominal_2250": ach_fwd / 2250.0,
-                     "flops_per_launch": flops_fwd, "ms_per_launch": fwd_ms},
-        "roofline_bwd": {"bound": "tensor", "kernels": "umma_kernel<DzEpi> + <StoreEpi> dH + <StoreEpi> dW",
-                         "achieved": 2 * flops_fwd / (bwd_ms / 1e3) / 1e12, "executed": 3 * flops_fwd / (bwd_ms / 1e3) / 1e12,
-                         "peak": peaks["sustained"], "unit": "TFLOP/s",
-                         "frac": 2 * flops_fwd / (bwd_ms / 1e3) / 1e12 / peaks["sustained"], "ms": bwd_ms,
-                         "note": "achieved counts the algorithmic 4MVd (dH, dW); executed adds the 2MVd logit recompute"},
-        "roofline_fused": {"achieved": 3 * flops_fwd / ((fwd_ms + bwd_ms) / 1e3) / 1e12, "unit": "TFLOP/s",
-                           "frac_of_sustained": 3 * flops_fwd / ((fwd_ms + bwd_ms) / 1e3) / 1e12 / peaks["sustained"],
-                           "frac_of_burst": 3 * flops_fwd / ((fwd_ms + bwd_ms) / 1e3) / 1e12 / peaks["burst"],
-                           "frac_of_nominal_2250": 3 * flops_fwd / ((fwd_ms + bwd_ms) / 1e3) / 1e12 / 2250.0,
-                           "note": "algorithmic 6MVd over forward + backward time"},
+        "parity": "green: every -m gpu test compares the CUDA path with the fp32 oracle / HF fixtures (tests/)",
+        "roofline": {"bound": "tensor", "kernel": dom_desc, "achieved": tf(tensor_ms[dom]), "peak": peaks["sustained"],
+                     "unit": "TFLOP/s", "frac": tf(tensor_ms[dom]) / peaks["sustained"], "traffic": traffic,
+                     "peak_source": f"{peaks['src']} sustained bf16 (kernel timed inside a long step)",
+                     "frac_of_burst": tf(tensor_ms[dom]) / peaks["burst"], "frac_of_nominal_2250": tf(tensor_ms[dom]) / 2250.0,
+                     "flops_per_step": flops_gemm, "ms_per_step": tensor_ms[dom],
+                     "launches_per_step": kern[dom]["launches_per_step"],
+                     "how": "ftk_timeline: CUDA events around every launch inside the timed steps, on the launch stream"},
+        "roofline_kernels": {k: {"achieved_tflops": tf(v), "frac_of_sustained": tf(v) / peaks["sustained"],
+                                 "ms_per_step": v} for k, v in tensor_ms.items()},
+        "roofline_fused": {"achieved": 3 * flops_gemm / (fused_ms / 1e3) / 1e12, "unit": "TFLOP/s",
+                           "frac_of_sustained": 3 * flops_gemm / (fused_ms / 1e3) / 1e12 / peaks["sustained"],
+                           "frac_of_burst": 3 * flops_gemm / (fused_ms / 1e3) / 1e12 / peaks["burst"],
+                           "frac_of_nominal_2250": 3 * flops_gemm / (fused_ms / 1e3) / 1e12 / 2250.0,
+                           "ms": fused_ms,
+                           "note": "algorithmic 6MVd over the kernels of the fused forward+backward (no recompute: "
+                                   "executed = algorithmic)"},
+        "roofline_convert": ({"bound": "hbm", "achieved": 4.0 * M * ((VOCAB + 63) // 64 * 64) / (conv["ms_per_step"] / 1e3) / 1e9,
+                              "peak": peaks["hbm"], "unit": "GB/s", "ms_per_step": conv["ms_per_step"],
+                              "note": "bf16 numerators -> dZ in place: 2 B read + 2 B written per (token, vocab) entry"}
+                             if conv else None),
         "roofline_gather": {"bound": "hbm", "achieved": gather_gbs, "peak": peaks["hbm"], "unit": "GB/s",
                             "frac": gather_gbs / peaks["hbm"],
                             "note": "bulk launch of 2^26 tokens drawn once each from a 134 MB source (> L2), 19 B/token, "
                                     "streaming stores, timed through the C ABI",
-                            "direct_variant_gbs": gather_direct_gbs, "plain_stores_gbs": gather_plain_gbs,},
-        "roofline_adamw": {"bound": "hbm", "achieved": adam_gbs, "peak": peaks["hbm"], "unit": "GB/s",
-                           "frac": adam_gbs / peaks["hbm"], "ms": adam_ms,
-                           "note": "grad-norm + clip + fused AdamW on the 103M-element bf16 lm_head bucket, 30 B/param; "
-                                   "not part of the timed step"},
-        "keep_mode": {"ms_per_step": keep_ms, "value": world * M / (keep_ms / 1e3), "unit": "tokens/s",
-                      "fused_algorithmic_tflops": 3 * flops_fwd / (keep_ms / 1e3) / 1e12,
-                      "note": "opt-in ops.set_backward_mode('keep'): the forward also stores bf16 softmax numerators "
-                              "(1.65 GB here) and the backward skips the logit recompute; not used for `value`"},
+                            "other_variant_gbs": gather_other_gbs, "plain_stores_gbs": gather_plain_gbs},
+        "roofline_adamw": ({"bound": "hbm",
+                            "achieved": ((32.0 if wire == "fp32" else 28.0) * VOCAB * D_MODEL) / (kern["adamw"]["ms_per_step"] / 1e3) / 1e9,
+                            "peak": peaks["hbm"], "unit": "GB/s", "ms_per_step": kern["adamw"]["ms_per_step"],
+                            "sqnorm_ms_per_step": kern.get("sqnorm", {}).get("ms_per_step"),
+                            "note": "fused AdamW on W inside the timed step: bf16 parameter, fp32 master and moments, "
+                                    f"{wire} gradient"} if "adamw" in kern else None),
+        "kernels_ms_per_step": {k: round(v["ms_per_step"], 4) for k, v in kern.items()},
+        "step_without_optimizer_ms": ms_noopt,
+        "recompute_mode": {"ms_per_step": recompute_ms, "value": world * M / (recompute_ms / 1e3), "unit": "tokens/s",
+                           "note": "ops.set_backward_mode('recompute'), round 1's default: forward keeps only lse, the "
+                                   "backward recomputes the logits (8MVd executed for 6MVd algorithmic); same step otherwise"},
         "e2e": {"value": e2e_value, "unit": "tokens/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms / args.steps,
-                "note": "token windows + hidden states from pinned host memory each step, loss and count read back"},
+                "note": "token windows + hidden states from pinned host memory each step, loss read back"},
         "gpu_launches": launches,
         "clocks": clocks,
     }
+    if world > 1:
+        line["exposed_comm_ms_per_step"] = exposed_comm_ms
+        line["allreduce_max_rel_err"] = allreduce_err
+        line["full_gradient_allreduce"] = full_grad
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = run_cpu_baseline()
     print(json.dumps(line), file=RESULT_OUT, flush=True)
     if world > 1:
+        tol = 1e-4 if wire == "fp32" else 1.5e-2
         dist.destroy_process_group()
+        if allreduce_err is None or not (allreduce_err <= tol):
+            print(f"all-reduce check failed: max relative error {allreduce_err} > {tol}", file=sys.stderr)
+            sys.exit(3)
 
 
 def _claim_stdout():

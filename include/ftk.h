@@ -67,6 +67,30 @@ const char* ftk_last_error(void);
 int ftk_set_option(int32_t key, int32_t value);
 
 /*
+ * Launch timeline: per-kernel device times inside a real step, without a profiler attached. No counterpart in
+ * the reference (its only timing is the wall clock per optimizer step, FT.py:496-535).
+ *   ftk_timeline_enable(1)  clears the timeline and starts recording: from now on every tagged launch is bracketed by
+ *                           two CUDA events on its own stream (host cost: two cudaEventRecord per launch)
+ *   ftk_timeline_enable(0)  stops recording and clears
+ *   ftk_timeline_read       waits for the recorded events, writes (tag, milliseconds) pairs in launch order and
+ *                           returns how many (<= max_n); negative on error. Do not call it during stream capture.
+ * Tags name the kernels of this library.
+ */
+#define FTK_TL_GATHER 1
+#define FTK_TL_FWD 2        /* fused lm_head GEMM + online softmax (ftk_lmhead_ce_fwd) */
+#define FTK_TL_FWD_KEEP 3   /* the same, also storing bf16 numerators */
+#define FTK_TL_FINALIZE 4
+#define FTK_TL_DZ 5         /* logit recompute + dZ (ftk_lmhead_ce_bwd) */
+#define FTK_TL_CONVERT 6    /* numerators -> dZ in place */
+#define FTK_TL_DH 7
+#define FTK_TL_DW 8
+#define FTK_TL_DBIAS 9
+#define FTK_TL_ADAMW 10
+#define FTK_TL_SQNORM 11
+int ftk_timeline_enable(int32_t on);
+int ftk_timeline_read(int32_t* tags, float* ms, int32_t max_n);
+
+/*
  * Window gather + label/mask construction, one launch per micro-batch.
  * Replaces TokenizedDataset.load (FT.py:662-692: slice, uint16->int64 widen,
  * mask rule), collector (FT.py:1030-1035: three stacks) and the label fill of
@@ -107,7 +131,8 @@ int ftk_gather_windows(const uint16_t* tokens, int64_t n_ctx, int32_t T, const i
  *   loss_sum fp32 [1] out: sum over valid rows of (lse - logit[target])
  *   n_valid  int32 [1] out: number of rows with target != -100
  *            (mean loss = loss_sum / n_valid; NaN when n_valid == 0, as in the reference)
- * Requirements: d % 64 == 0, H/W 16-byte aligned.
+ * Requirements: d % 64 == 0, H/W 16-byte aligned. Every target must be -100 or lie in [0, V): a target >= V (the
+ * uint16 token file can hold ids up to 65535) makes loss_sum NaN, where torch's cross_entropy raises a device assert.
  */
 size_t ftk_lmhead_ce_fwd_workspace(int64_t M, int32_t d, int32_t V);
 int ftk_lmhead_ce_fwd(const void* H, const void* W, const void* bias, const int64_t* targets, int64_t M, int32_t d,
@@ -185,6 +210,46 @@ int ftk_lmhead_ce_bwd(const void* H, const void* W, const void* bias, const int6
                       float* dbias, void* workspace, size_t workspace_bytes, void* stream);
 
 /*
+ * Forward and backward of lm_head + cross-entropy in ONE call, for training steps (the default path of
+ * ops.fused_lmhead_ce when gradients are wanted). Replaces the same reference code as ftk_lmhead_ce_fwd and
+ * ftk_lmhead_ce_bwd together (FT.py:479 and the loss.backward() that follows it); the reference has no such
+ * combined call.
+ *
+ * Doing both at once removes the logit recompute of ftk_lmhead_ce_bwd (a quarter of a step's tensor work) without
+ * keeping anything of size [tokens x vocab] between forward and backward: the rows are processed in slabs, and for
+ * each slab the forward sweep leaves bf16 softmax numerators in the workspace, a finalize pass gives lse, one
+ * HBM-bound pass turns the numerators into dZ in place, and the dH and dW GEMMs consume them before the next slab
+ * overwrites them. The numerators slab is capped at 1 GiB whatever M is (at most 10,496 rows at V = 50,257);
+ * ftk_lmhead_ce_fused_slab_rows reports the rows per slab the library would pick (slab_rows = 0) or clamps a
+ * request.
+ *
+ *   dZ scale   grad_scale * (grad_scale_dev ? *grad_scale_dev : 1) / n_valid, with n_valid counted from `targets` at
+ *              the start of the call. A caller that only learns the upstream gradient later (autograd) passes 1 and
+ *              rescales dH / dW afterwards (ftk_scale_unless_one).
+ *   dH         bf16 [M,d] out
+ *   dW         [V,d] bf16 / fp32, accumulate != 0 adds into it (tied embeddings, gradient accumulation, fp32 main
+ *              gradients); dbias fp32 [V] or NULL likewise
+ *   dw_done_event   a cudaEvent_t, or NULL. When given, the last slab runs its dW GEMM before its dH GEMM, records
+ *              the event on `stream` between the two, and launches that dH GEMM on (SMs - FTK_OPT_SM_RESERVE) SMs:
+ *              dW is complete once the event fires, so a data-parallel caller hands the event to
+ *              ftk_dp_allreduce_after and the all-reduce of dW runs on the idle SMs while dH is still being
+ *              computed. Every other launch of the call uses all SMs.
+ *   lse, loss_sum, n_valid   as ftk_lmhead_ce_fwd
+ *
+ * ftk_scale_unless_one multiplies n elements (FTK_BF16 / FTK_F32, 16-byte aligned, n a multiple of 8 / 4) by the
+ * device scalar *factor_dev and does nothing when that scalar is exactly 1; with poison != 0 the elements become
+ * NaN instead when the scalar is not 1 (for gradients that were already added into a caller's buffer and cannot be
+ * rescaled: a wrong assumption then shows instead of passing silently).
+ */
+int64_t ftk_lmhead_ce_fused_slab_rows(int64_t M, int32_t d, int32_t V, int64_t slab_rows);
+size_t ftk_lmhead_ce_fused_workspace(int64_t M, int32_t d, int32_t V, int64_t slab_rows);
+int ftk_lmhead_ce_fused(const void* H, const void* W, const void* bias, const int64_t* targets, int64_t M, int32_t d,
+                        int32_t V, float grad_scale, const float* grad_scale_dev, float* lse, float* loss_sum,
+                        int32_t* n_valid, void* dH, void* dW, int32_t dw_dtype, int32_t accumulate, float* dbias,
+                        void* dw_done_event, void* workspace, size_t workspace_bytes, int64_t slab_rows, void* stream);
+int ftk_scale_unless_one(void* buf, size_t n, int32_t dtype, const float* factor_dev, int32_t poison, void* stream);
+
+/*
  * Data-parallel gradient all-reduce (replaces DeepSpeed ZeRO's bucketed
  * gradient reduction configured by finetuner/ds_config.json:27-45 and enabled
  * at FT.py:911-923). One communicator + one high-priority comm stream per rank.
@@ -194,6 +259,9 @@ int ftk_lmhead_ce_bwd(const void* H, const void* W, const void* bias, const int6
  *   ftk_dp_allreduce  on the comm stream: wait for `ready_stream` work issued so far,
  *                     multiply by prescale (1/world for the reference's mean), ncclAllReduce(sum)
  *                     in place over `count` elements of dtype (FTK_BF16/FTK_F32); never blocks the host
+ *   ftk_dp_allreduce_after  the same, but the bucket is ready when `ready_event` (a cudaEvent_t the caller had
+ *                     recorded, e.g. ftk_lmhead_ce_fused's dw_done_event) fires: the collective can start while the
+ *                     producing stream is still busy with later work
  *   ftk_dp_join       makes `stream` wait for everything issued on the comm stream so far
  *   ftk_set_sm_reserve  process-wide: the persistent lm_head kernels launched after this call leave n_sms SMs
  *                     idle (0 = use all). A NCCL kernel cannot share an SM with them, so without a reserve an
@@ -206,6 +274,7 @@ typedef struct ftk_dp ftk_dp_t;
 int ftk_dp_unique_id(void* id128_host);
 int ftk_dp_init(const void* id128_host, int32_t rank, int32_t world, ftk_dp_t** out);
 int ftk_dp_allreduce(ftk_dp_t* dp, void* buf, size_t count, int32_t dtype, float prescale, void* ready_stream);
+int ftk_dp_allreduce_after(ftk_dp_t* dp, void* buf, size_t count, int32_t dtype, float prescale, void* ready_event);
 int ftk_dp_join(ftk_dp_t* dp, void* stream);
 int ftk_dp_destroy(ftk_dp_t* dp);
 
@@ -222,7 +291,9 @@ int ftk_dp_destroy(ftk_dp_t* dp);
  *   ftk_clip_coef    coef[0] = min(1, max_norm / (sqrt(sqnorm[0]) + 1e-6))  (clip_grad_norm_)
  *   ftk_adamw_step   one AdamW update of n elements; step counts from 1.
  *                    param FTK_F32: updated in place (grad FTK_F32 or FTK_BF16, master unused);
- *                    param FTK_BF16: `master` (fp32) is updated and param is its bf16 rounding.
+ *                    param FTK_BF16: `master` (fp32) is updated and param is its bf16 rounding (grad FTK_BF16, or
+ *                    FTK_F32 for fp32 main gradients: the reference accumulates and reduces gradients in fp32,
+ *                    ds_config.json:45).
  *                    Every gradient is first multiplied by grad_scale * (grad_scale_dev ? *grad_scale_dev : 1).
  */
 size_t ftk_grad_sqnorm_workspace(void);

@@ -34,15 +34,24 @@ SIGNATURES = {
                                          c_void_p, c_void_p]),
     "ftk_lmhead_ce_fwd_static": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p,
                                            c_void_p, c_void_p, c_void_p]),
+    "ftk_lmhead_ce_fused_slab_rows": (c_int64, [c_int64, c_int32, c_int32, c_int64]),
+    "ftk_lmhead_ce_fused_workspace": (c_size_t, [c_int64, c_int32, c_int32, c_int64]),
+    "ftk_lmhead_ce_fused": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_float,
+                                      c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int32,
+                                      c_void_p, c_void_p, c_void_p, c_size_t, c_int64, c_void_p]),
+    "ftk_scale_unless_one": (c_int32, [c_void_p, c_size_t, c_int32, c_void_p, c_int32, c_void_p]),
     "ftk_lmhead_ce_bwd_workspace": (c_size_t, [c_int64, c_int32, c_int32, c_int64]),
     "ftk_lmhead_ce_bwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32,
                                     c_float, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_void_p,
                                     c_void_p, c_size_t, c_void_p]),
     "ftk_set_option": (c_int32, [c_int32, c_int32]),
+    "ftk_timeline_enable": (c_int32, [c_int32]),
+    "ftk_timeline_read": (c_int32, [c_void_p, c_void_p, c_int32]),
     "ftk_set_sm_reserve": (c_int32, [c_int32]),
     "ftk_dp_unique_id": (c_int32, [c_void_p]),
     "ftk_dp_init": (c_int32, [c_void_p, c_int32, c_int32, POINTER(c_void_p)]),
     "ftk_dp_allreduce": (c_int32, [c_void_p, c_void_p, c_size_t, c_int32, c_float, c_void_p]),
+    "ftk_dp_allreduce_after": (c_int32, [c_void_p, c_void_p, c_size_t, c_int32, c_float, c_void_p]),
     "ftk_dp_join": (c_int32, [c_void_p, c_void_p]),
     "ftk_dp_destroy": (c_int32, [c_void_p]),
     "ftk_grad_sqnorm_workspace": (c_size_t, []),
@@ -102,3 +111,21 @@ def set_option(name: str, value: int) -> None:
     """ftk_set_option by name: "cta_group" (1|2), "gather_variant" (0 auto|1 direct), "gather_stores"
     (0 auto|1 streaming|2 plain), "sm_reserve" (0..64)."""
     check(lib().ftk_set_option(OPTIONS[name], int(value)), f"ftk_set_option({name})")
+
+
+TIMELINE_TAGS = {1: "gather", 2: "fwd", 3: "fwd_keep", 4: "finalize", 5: "dz", 6: "convert", 7: "dH", 8: "dW",
+                 9: "dbias", 10: "adamw", 11: "sqnorm"}  # FTK_TL_* in include/ftk.h
+
+
+def timeline_enable(on: bool) -> None:
+    check(lib().ftk_timeline_enable(int(on)), "ftk_timeline_enable")
+
+
+def timeline_read(max_n: int = 1 << 16):
+    """[(kernel name, milliseconds)] for every tagged launch since ``timeline_enable(True)``; waits for them."""
+    tags = (c_int32 * max_n)()
+    ms = (c_float * max_n)()
+    n = lib().ftk_timeline_read(tags, ms, max_n)
+    if n < 0:
+        check(n, "ftk_timeline_read")
+    return [(TIMELINE_TAGS.get(tags[i], str(tags[i])), ms[i]) for i in range(n)]

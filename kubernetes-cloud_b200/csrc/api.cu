@@ -1,5 +1,7 @@
 // ABI version, thread-local error text, cached device facts.
 #include <atomic>
+#include <mutex>
+#include <vector>
 
 #include "ftk_host.h"
 
@@ -34,6 +36,38 @@ std::atomic<int> g_options[FTK_OPT_COUNT_] = {{2}, {0}, {0}, {0}};  // cta_group
 
 int option(int key) { return g_options[key].load(std::memory_order_relaxed); }
 
+// ---- launch timeline
+namespace {
+struct TimelineEntry {
+  int tag;
+  cudaEvent_t a, b;
+};
+std::atomic<int> g_tl_on{0};
+std::mutex g_tl_mu;
+std::vector<TimelineEntry> g_tl;
+constexpr size_t kTimelineCap = 1 << 16;
+}  // namespace
+
+bool timeline_on() { return g_tl_on.load(std::memory_order_relaxed) != 0; }
+
+void timeline_mark(int tag, cudaStream_t st, bool begin) {
+  std::lock_guard<std::mutex> lk(g_tl_mu);
+  if (begin) {
+    if (g_tl.size() >= kTimelineCap) return;
+    TimelineEntry e{tag, nullptr, nullptr};
+    if (cudaEventCreate(&e.a) != cudaSuccess || cudaEventCreate(&e.b) != cudaSuccess) return;
+    cudaEventRecord(e.a, st);
+    g_tl.push_back(e);
+  } else {
+    // the matching begin is the latest open entry with this tag
+    for (size_t i = g_tl.size(); i-- > 0;)
+      if (g_tl[i].tag == tag) {
+        cudaEventRecord(g_tl[i].b, st);
+        break;
+      }
+  }
+}
+
 }  // namespace ftk
 
 extern "C" int ftk_set_option(int32_t key, int32_t value) {
@@ -56,6 +90,33 @@ extern "C" int ftk_set_option(int32_t key, int32_t value) {
   }
   ftk::g_options[key].store(value, std::memory_order_relaxed);
   return FTK_OK;
+}
+
+extern "C" int ftk_timeline_enable(int32_t on) {
+  std::lock_guard<std::mutex> lk(ftk::g_tl_mu);
+  for (auto& e : ftk::g_tl) {
+    cudaEventDestroy(e.a);
+    cudaEventDestroy(e.b);
+  }
+  ftk::g_tl.clear();
+  ftk::g_tl_on.store(on ? 1 : 0, std::memory_order_relaxed);
+  return FTK_OK;
+}
+
+extern "C" int ftk_timeline_read(int32_t* tags, float* ms, int32_t max_n) {
+  FTK_REQUIRE(tags && ms && max_n >= 0, "ftk_timeline_read: bad arguments");
+  std::lock_guard<std::mutex> lk(ftk::g_tl_mu);
+  int n = 0;
+  for (auto& e : ftk::g_tl) {
+    if (n >= max_n) break;
+    FTK_CUDA_CHECK(cudaEventSynchronize(e.b));
+    float t = 0.f;
+    FTK_CUDA_CHECK(cudaEventElapsedTime(&t, e.a, e.b));
+    tags[n] = e.tag;
+    ms[n] = t;
+    ++n;
+  }
+  return n;
 }
 
 extern "C" int ftk_set_sm_reserve(int32_t n_sms) { return ftk_set_option(FTK_OPT_SM_RESERVE, n_sms); }

@@ -184,6 +184,8 @@ extern "C" int ftk_dp_init(const void* id128_host, int32_t rank, int32_t world, 
   return FTK_OK;
 }
 
+static int allreduce_on_comm_stream(ftk_dp_t* dp, void* buf, size_t count, int32_t dtype, float prescale);
+
 extern "C" int ftk_dp_allreduce(ftk_dp_t* dp, void* buf, size_t count, int32_t dtype, float prescale,
                                 void* ready_stream) {
   FTK_REQUIRE(dp && buf, "ftk_dp_allreduce: null pointer argument");
@@ -193,6 +195,21 @@ extern "C" int ftk_dp_allreduce(ftk_dp_t* dp, void* buf, size_t count, int32_t d
   // the bucket is ready once everything issued so far on ready_stream has run
   FTK_CUDA_CHECK(cudaEventRecord(dp->ev_ready, static_cast<cudaStream_t>(ready_stream)));
   FTK_CUDA_CHECK(cudaStreamWaitEvent(dp->comm_stream, dp->ev_ready, 0));
+  return allreduce_on_comm_stream(dp, buf, count, dtype, prescale);
+}
+
+extern "C" int ftk_dp_allreduce_after(ftk_dp_t* dp, void* buf, size_t count, int32_t dtype, float prescale,
+                                      void* ready_event) {
+  FTK_REQUIRE(dp && buf && ready_event, "ftk_dp_allreduce_after: null pointer argument");
+  FTK_REQUIRE(dtype == FTK_BF16 || dtype == FTK_F32, "ftk_dp_allreduce_after: bad dtype %d", dtype);
+  FTK_REQUIRE((reinterpret_cast<uintptr_t>(buf) & 15) == 0, "ftk_dp_allreduce_after: buffer %p is not 16-byte aligned",
+              buf);
+  if (count == 0) return FTK_OK;
+  FTK_CUDA_CHECK(cudaStreamWaitEvent(dp->comm_stream, static_cast<cudaEvent_t>(ready_event), 0));
+  return allreduce_on_comm_stream(dp, buf, count, dtype, prescale);
+}
+
+static int allreduce_on_comm_stream(ftk_dp_t* dp, void* buf, size_t count, int32_t dtype, float prescale) {
   // The scale is folded into the collective (ncclAvg for 1/world, a pre-multiplied sum otherwise): a separate
   // scaling kernel on the comm stream would have to squeeze through whatever SMs a concurrent persistent GEMM left
   // free and delays the all-reduce by about a millisecond (profiles/r01_overlap_probe.txt).

@@ -38,6 +38,22 @@ struct DeviceInfo {
 };
 int get_device_info(DeviceInfo* out);  // current device; FTK_OK or error
 
+// Launch timeline (ftk_timeline_*): when enabled, a pair of CUDA events brackets every tagged launch on its own
+// stream.  TimelineScope records the first event at construction and the second at destruction.
+bool timeline_on();
+void timeline_mark(int tag, cudaStream_t st, bool begin);
+struct TimelineScope {
+  int tag;
+  cudaStream_t st;
+  bool on;
+  TimelineScope(int t, cudaStream_t s) : tag(t), st(s), on(timeline_on()) {
+    if (on) timeline_mark(tag, st, true);
+  }
+  ~TimelineScope() {
+    if (on) timeline_mark(tag, st, false);
+  }
+};
+
 // Process-wide tuning options (ftk_set_option): read with a relaxed atomic load on every launch, never from the
 // environment.
 int option(int key);

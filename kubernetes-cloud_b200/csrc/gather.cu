@@ -269,6 +269,7 @@ extern "C" int ftk_gather_windows(const uint16_t* tokens, int64_t n_ctx, int32_t
   const int stores = ftk::option(FTK_OPT_GATHER_STORES);
   bool cs = static_cast<int64_t>(B) * T >= (int64_t(1) << 22);
   if (stores != 0) cs = (stores == 1);
+  ftk::TimelineScope tl_(FTK_TL_GATHER, st);
   if (T % 4 == 0 && aligned32 && (want_direct || T % 16 != 0)) {
     const int64_t n_pieces = static_cast<int64_t>(B) * ((T + kPiece - 1) / kPiece);
     const int64_t blocks = (n_pieces + kThreads / 32 - 1) / (kThreads / 32);

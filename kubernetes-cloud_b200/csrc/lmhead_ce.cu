@@ -673,7 +673,8 @@ __global__ void __launch_bounds__(256) fwd_finalize_kernel(const float* __restri
                                                            int V, int n_chunks, float* __restrict__ lse,
                                                            float* __restrict__ blk_loss, int* __restrict__ blk_cnt,
                                                            unsigned int* __restrict__ ticket,
-                                                           float* __restrict__ loss_sum, int* __restrict__ n_valid) {
+                                                           float* __restrict__ loss_sum, int* __restrict__ n_valid,
+                                                           int add_to_loss) {
   __shared__ float s_loss[8];
   __shared__ int s_cnt[8];
   __shared__ bool s_last;
@@ -731,9 +732,46 @@ __global__ void __launch_bounds__(256) fwd_finalize_kernel(const float* __restri
       tl += static_cast<double>(reinterpret_cast<volatile float*>(blk_loss)[b]);
       tc += reinterpret_cast<volatile int*>(blk_cnt)[b];
     }
-    *loss_sum = static_cast<float>(tl);
-    *n_valid = tc;
+    // add_to_loss: this launch covers one slab of rows of a larger call; slabs run one after another on the stream
+    *loss_sum = add_to_loss ? *loss_sum + static_cast<float>(tl) : static_cast<float>(tl);
+    if (n_valid != nullptr) *n_valid = tc;
     *ticket = 0u;
+  }
+}
+
+// n_valid = number of targets >= 0 (out must be zero on entry; integer atomics, so the result is exact).
+__global__ void __launch_bounds__(256) count_valid_kernel(const int64_t* __restrict__ targets, int64_t M,
+                                                          int32_t* __restrict__ out) {
+  int c = 0;
+  for (int64_t i = blockIdx.x * 256ll + threadIdx.x; i < M; i += gridDim.x * 256ll) c += (targets[i] >= 0) ? 1 : 0;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
+  if ((threadIdx.x & 31) == 0 && c != 0) atomicAdd(out, c);
+}
+
+// buf[i] *= *factor unless the factor is exactly 1 (then every block leaves at once): the fix-up the fused
+// forward+backward needs when the upstream gradient turns out not to be the 1.0 it assumed.
+template <typename T>
+__global__ void __launch_bounds__(256) scale_unless_one_kernel(T* __restrict__ buf, size_t n_vec,
+                                                               const float* __restrict__ factor, int poison) {
+  float f = __ldg(factor);
+  if (f == 1.0f) return;
+  if (poison) f = __int_as_float(0x7fc00000);
+  uint4* b = reinterpret_cast<uint4*>(buf);
+  for (size_t i = blockIdx.x * static_cast<size_t>(256) + threadIdx.x; i < n_vec; i += gridDim.x * static_cast<size_t>(256)) {
+    uint4 v = b[i];
+    uint32_t* w = reinterpret_cast<uint32_t*>(&v);
+    if constexpr (sizeof(T) == 4) {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) w[e] = __float_as_uint(__uint_as_float(w[e]) * f);
+    } else {
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&w[e]);
+        w[e] = pack_bf16x2(__low2float(h) * f, __high2float(h) * f);
+      }
+    }
+    b[i] = v;
   }
 }
 
@@ -854,7 +892,7 @@ inline int sm_reserve() { return ftk::option(FTK_OPT_SM_RESERVE); }
 
 template <int kCG, int BN, int kStages, bool kAMN, bool kBMN, class Epi>
 int launch_umma(const CUtensorMap& tmA, const CUtensorMap& tmB, const Sched& sc, const typename Epi::Params& ep,
-                int sm_count, cudaStream_t st) {
+                int sm_count, cudaStream_t st, int reserve = -1) {
   using L = SmemLayout<kCG, BN, kStages, Epi::kSmemBytes>;
   auto kern = umma_kernel<kCG, BN, kStages, kAMN, kBMN, Epi>;
   static bool attr_done[64] = {false};  // per instantiation and device
@@ -864,7 +902,7 @@ int launch_umma(const CUtensorMap& tmA, const CUtensorMap& tmB, const Sched& sc,
     FTK_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(L::BYTES)));
     attr_done[dev & 63] = true;
   }
-  int usable = sm_count - sm_reserve();
+  int usable = sm_count - (reserve >= 0 ? reserve : sm_reserve());
   if (usable < kCG) usable = kCG;
   int n_cl = usable / kCG;
   if (n_cl > sc.n_units) n_cl = sc.n_units;
@@ -993,10 +1031,13 @@ int run_fwd(const void* H, const void* W, const void* bias, const int64_t* targe
   ep.V = V;
   ep.Mpad = static_cast<int>(ws.Mpad);
   FTK_CUDA_CHECK(cudaMemsetAsync(ws.ticket, 0, sizeof(unsigned int), st));
-  if (int rc = launch_umma<kCG, BN, kStages, false, false, FwdEpi>(tmA, tmB, sc, ep, sm_count, st)) return rc;
+{
+    ftk::TimelineScope tl_(FTK_TL_FWD, st);
+    if (int rc = launch_umma<kCG, BN, kStages, false, false, FwdEpi>(tmA, tmB, sc, ep, sm_count, st)) return rc;
+  }
   fwd_finalize_kernel<<<ceil_div(M, 256), 256, 0, st>>>(ws.pmax, ws.psum, ws.ztgt, targets, static_cast<int>(M),
                                                         static_cast<int>(ws.Mpad), V, n_chunks, lse, ws.blk_loss,
-                                                        ws.blk_cnt, ws.ticket, loss_sum, n_valid);
+                                                        ws.blk_cnt, ws.ticket, loss_sum, n_valid, 0);
   FTK_CUDA_CHECK(cudaGetLastError());
   return FTK_OK;
 }
@@ -1005,7 +1046,7 @@ int run_fwd(const void* H, const void* W, const void* bias, const int64_t* targe
 template <int kCG>
 int run_fwd_keep(const void* H, const void* W, const void* bias, const int64_t* targets, int64_t M, int d, int V,
                  float* lse, float* loss_sum, int32_t* n_valid, __nv_bfloat16* probs, float* cref,
-                 const FwdWorkspace& ws, int sm_count, cudaStream_t st) {
+                 const FwdWorkspace& ws, int sm_count, cudaStream_t st, int add_to_loss = 0) {
   constexpr int BN = 256;
   constexpr int kStages = (kCG == 1) ? 4 : 6;
   const int64_t ld = round_up(V, 64);
@@ -1037,10 +1078,13 @@ int run_fwd_keep(const void* H, const void* W, const void* bias, const int64_t* 
   ep.Mpad = static_cast<int>(ws.Mpad);
   ep.ld = static_cast<int>(ld);
   FTK_CUDA_CHECK(cudaMemsetAsync(ws.ticket, 0, sizeof(unsigned int), st));
-  if (int rc = launch_umma<kCG, BN, kStages, false, false, FwdKeepEpi>(tmA, tmB, sc, ep, sm_count, st)) return rc;
+{
+    ftk::TimelineScope tl_(FTK_TL_FWD_KEEP, st);
+    if (int rc = launch_umma<kCG, BN, kStages, false, false, FwdKeepEpi>(tmA, tmB, sc, ep, sm_count, st)) return rc;
+  }
   fwd_finalize_kernel<<<ceil_div(M, 256), 256, 0, st>>>(ws.pmax, ws.psum, ws.ztgt, targets, static_cast<int>(M),
                                                         static_cast<int>(ws.Mpad), V, n_chunks, lse, ws.blk_loss,
-                                                        ws.blk_cnt, ws.ticket, loss_sum, n_valid);
+                                                        ws.blk_cnt, ws.ticket, loss_sum, n_valid, add_to_loss);
   FTK_CUDA_CHECK(cudaGetLastError());
   return FTK_OK;
 }
@@ -1048,9 +1092,20 @@ int run_fwd_keep(const void* H, const void* W, const void* bias, const int64_t* 
 constexpr int64_t kDefaultSlabRows = 16384;
 inline int64_t dz_pitch(int V) { return round_up(V, 64); }  // bf16 elements; rows start 128-byte aligned
 
+// How the two gradient GEMMs of one slab are issued.  Default: dH then dW, both on `sm_count - FTK_OPT_SM_RESERVE`
+// SMs.  overlap_tail (the last slab of a data-parallel caller's fused call): dW first on every SM, `dw_done`
+// recorded behind it, then dH on `sm_count - FTK_OPT_SM_RESERVE` SMs, so the all-reduce of dW can start on the SMs
+// dH leaves idle while dH is still running.
+struct GradGemmPlan {
+  bool overlap_tail = false;
+  bool full_sms = false;  // ignore the SM reserve for both GEMMs (slabs whose gradients nobody is waiting for yet)
+  cudaEvent_t dw_done = nullptr;
+};
+
 template <int kCG>
 int run_grad_gemms(const void* H, const void* W, int64_t rows, int d, int V, void* dH, void* dW, int dw_dtype,
-                   int accumulate, float* dbias, __nv_bfloat16* dz, int sm_count, cudaStream_t st);
+                   int accumulate, float* dbias, __nv_bfloat16* dz, int sm_count, cudaStream_t st,
+                   const GradGemmPlan& plan);
 
 template <int kCG>
 int run_bwd_slab(const void* H, const void* W, const void* bias, const int64_t* targets, const float* lse,
@@ -1089,79 +1144,120 @@ int run_bwd_slab(const void* H, const void* W, const void* bias, const int64_t* 
     ep.rows = static_cast<int>(rows);
     ep.V = V;
     ep.ld = static_cast<int>(ld);
+    ftk::TimelineScope tl_(FTK_TL_DZ, st);
     if (int rc = launch_umma<kCG, BN, kStages, false, false, DzEpi>(tmA, tmB, sc, ep, sm_count, st)) return rc;
   }
-  return run_grad_gemms<kCG>(H, W, rows, d, V, dH, dW, dw_dtype, accumulate, dbias, dz, sm_count, st);
+  return run_grad_gemms<kCG>(H, W, rows, d, V, dH, dW, dw_dtype, accumulate, dbias, dz, sm_count, st, GradGemmPlan());
+}
+
+// dH[rows, d] = dZ[rows, V] . W[V, d]: A K-major (K = V, the tail zero-filled by TMA), B MN-major.
+template <int kCG, int BN>
+int run_dh(const void* W, int64_t rows, int d, int V, void* dH, __nv_bfloat16* dz, int sm_count, cudaStream_t st,
+           int reserve) {
+  constexpr int kStages = (BN == 256) ? ((kCG == 1) ? 4 : 6) : ((kCG == 1) ? 6 : 8);
+  const int64_t ld = dz_pitch(V);
+  CUtensorMap tmA, tmB;
+  if (int rc = make_tmap(&tmA, dz, V, rows, static_cast<uint64_t>(ld) * 2, BK, BM)) return rc;
+  if (int rc = make_tmap(&tmB, W, d, V, static_cast<uint64_t>(d) * 2, 64, BK)) return rc;
+  Sched sc;
+  const int n_mblk = ceil_div(rows, BM * kCG);
+  sc.n_ntile = ceil_div(d, BN);
+  sc.tiles_per_chunk = 1;
+  sc.n_units = n_mblk * sc.n_ntile;
+  sc.n_mblk = n_mblk;
+  sc.n_chunks = sc.n_ntile;
+  sc.m_group = 1;  // N tiles of one m block are adjacent: the dZ rows are read from HBM once
+  sc.n_kblk = ceil_div(V, BK);
+  pick_hints("nnn", 2, &sc.hint_a, &sc.hint_b, nullptr);
+  StoreEpi<false>::Params ep;
+  ep.out = dH;
+  ep.rows = static_cast<int>(rows);
+  ep.cols = d;
+  ep.ld = d;
+  ep.accumulate = 0;
+  ftk::TimelineScope tl_(FTK_TL_DH, st);
+  return launch_umma<kCG, BN, kStages, false, true, StoreEpi<false>>(tmA, tmB, sc, ep, sm_count, st, reserve);
+}
+
+// dW[V, d] (+)= dZ^T[V, rows] . H[rows, d]: A and B MN-major.
+template <int kCG>
+int run_dw(const void* H, int64_t rows, int d, int V, void* dW, int dw_dtype, int accumulate, __nv_bfloat16* dz,
+           int sm_count, cudaStream_t st, int reserve) {
+  constexpr int BN = 256;
+  constexpr int kStages = (kCG == 1) ? 4 : 6;
+  const int64_t ld = dz_pitch(V);
+  CUtensorMap tmA, tmB;
+  if (int rc = make_tmap(&tmA, dz, V, rows, static_cast<uint64_t>(ld) * 2, 64, BK)) return rc;
+  if (int rc = make_tmap(&tmB, H, d, rows, static_cast<uint64_t>(d) * 2, 64, BK)) return rc;
+  Sched sc;
+  const int n_mblk = ceil_div(V, BM * kCG);
+  sc.n_ntile = ceil_div(d, BN);
+  sc.tiles_per_chunk = 1;
+  sc.n_units = n_mblk * sc.n_ntile;
+  sc.n_mblk = n_mblk;
+  sc.n_chunks = sc.n_ntile;
+  sc.m_group = 1;
+  sc.n_kblk = ceil_div(rows, BK);
+  pick_hints("nnn", 3, &sc.hint_a, &sc.hint_b, nullptr);
+  ftk::TimelineScope tl_(FTK_TL_DW, st);
+  if (dw_dtype == FTK_F32) {
+    StoreEpi<true>::Params ep;
+    ep.out = dW;
+    ep.rows = V;
+    ep.cols = d;
+    ep.ld = d;
+    ep.accumulate = accumulate;
+    return launch_umma<kCG, BN, kStages, true, true, StoreEpi<true>>(tmA, tmB, sc, ep, sm_count, st, reserve);
+  }
+  StoreEpi<false>::Params ep;
+  ep.out = dW;
+  ep.rows = V;
+  ep.cols = d;
+  ep.ld = d;
+  ep.accumulate = accumulate;
+  return launch_umma<kCG, BN, kStages, true, true, StoreEpi<false>>(tmA, tmB, sc, ep, sm_count, st, reserve);
+}
+
+// Tile width of the dH GEMM.  Its units are (row block x N tile) with the whole vocabulary as K, so few rows give
+// few, long units.  128-wide tiles double the unit count but move 1.5x the operand bytes per flop from L2 to shared
+// memory, which is what bounds these kernels at full clock: measured 1.6x slower per flop (8192 rows, d = 2048:
+// 7 half-waves of 128 took 3.9 ms against 2.8 ms for 4 waves of 256).  They pay only when the 256-wide launch would
+// leave most SM pairs idle (a few hundred rows).
+constexpr int kNarrowTilePenaltyPct = 160;
+inline int pick_dh_bn(int64_t rows, int d, int n_groups, int kCG) {
+  const int64_t n_mblk = ceil_div(rows, BM * kCG);
+  const int64_t w256 = ceil_div(n_mblk * ceil_div(d, 256), n_groups) * 2;
+  const int64_t w128 = ceil_div(n_mblk * ceil_div(d, 128), n_groups);
+  return (w128 * kNarrowTilePenaltyPct < w256 * 100) ? 128 : 256;
 }
 
 template <int kCG>
 int run_grad_gemms(const void* H, const void* W, int64_t rows, int d, int V, void* dH, void* dW, int dw_dtype,
-                   int accumulate, float* dbias, __nv_bfloat16* dz, int sm_count, cudaStream_t st) {
-  constexpr int BN = 256;
-  constexpr int kStages = (kCG == 1) ? 4 : 6;
-  const int64_t ld = dz_pitch(V);
-  // ---- stage 2: dH[rows, d] = dZ[rows, V] . W[V, d]
-  {
-    CUtensorMap tmA, tmB;
-    if (int rc = make_tmap(&tmA, dz, V, rows, static_cast<uint64_t>(ld) * 2, BK, BM)) return rc;
-    if (int rc = make_tmap(&tmB, W, d, V, static_cast<uint64_t>(d) * 2, 64, BK)) return rc;
-    Sched sc;
-    const int n_mblk = ceil_div(rows, BM * kCG);
-    sc.n_ntile = ceil_div(d, BN);
-    sc.tiles_per_chunk = 1;
-    sc.n_units = n_mblk * sc.n_ntile;
-    sc.n_mblk = n_mblk;
-    sc.n_chunks = sc.n_ntile;
-    sc.m_group = 1;  // N tiles of one m block are adjacent: the dZ rows are read from HBM once
-    sc.n_kblk = ceil_div(V, BK);
-    pick_hints("nnn", 2, &sc.hint_a, &sc.hint_b, nullptr);
-    StoreEpi<false>::Params ep;
-    ep.out = dH;
-    ep.rows = static_cast<int>(rows);
-    ep.cols = d;
-    ep.ld = d;
-    ep.accumulate = 0;
-    if (int rc = launch_umma<kCG, BN, kStages, false, true, StoreEpi<false>>(tmA, tmB, sc, ep, sm_count, st)) return rc;
+                   int accumulate, float* dbias, __nv_bfloat16* dz, int sm_count, cudaStream_t st,
+                   const GradGemmPlan& plan) {
+  const int res_dh = plan.full_sms ? 0 : -1;
+  const int res_dw = (plan.full_sms || plan.overlap_tail) ? 0 : -1;
+  const int usable = sm_count - (res_dh == 0 ? 0 : sm_reserve());
+  const int n_groups = (usable > kCG ? usable : kCG) / kCG;
+  const int dh_bn = pick_dh_bn(rows, d, n_groups, kCG);
+  if (plan.overlap_tail) {
+    if (int rc = run_dw<kCG>(H, rows, d, V, dW, dw_dtype, accumulate, dz, sm_count, st, res_dw)) return rc;
+    if (plan.dw_done != nullptr) FTK_CUDA_CHECK(cudaEventRecord(plan.dw_done, st));
   }
-  // ---- stage 3: dW[V, d] (+)= dZ^T[V, rows] . H[rows, d]
-  {
-    CUtensorMap tmA, tmB;
-    if (int rc = make_tmap(&tmA, dz, V, rows, static_cast<uint64_t>(ld) * 2, 64, BK)) return rc;
-    if (int rc = make_tmap(&tmB, H, d, rows, static_cast<uint64_t>(d) * 2, 64, BK)) return rc;
-    Sched sc;
-    const int n_mblk = ceil_div(V, BM * kCG);
-    sc.n_ntile = ceil_div(d, BN);
-    sc.tiles_per_chunk = 1;
-    sc.n_units = n_mblk * sc.n_ntile;
-    sc.n_mblk = n_mblk;
-    sc.n_chunks = sc.n_ntile;
-    sc.m_group = 1;
-    sc.n_kblk = ceil_div(rows, BK);
-    pick_hints("nnn", 3, &sc.hint_a, &sc.hint_b, nullptr);
-    if (dw_dtype == FTK_F32) {
-      StoreEpi<true>::Params ep;
-      ep.out = dW;
-      ep.rows = V;
-      ep.cols = d;
-      ep.ld = d;
-      ep.accumulate = accumulate;
-      if (int rc = launch_umma<kCG, BN, kStages, true, true, StoreEpi<true>>(tmA, tmB, sc, ep, sm_count, st)) return rc;
-    } else {
-      StoreEpi<false>::Params ep;
-      ep.out = dW;
-      ep.rows = V;
-      ep.cols = d;
-      ep.ld = d;
-      ep.accumulate = accumulate;
-      if (int rc = launch_umma<kCG, BN, kStages, true, true, StoreEpi<false>>(tmA, tmB, sc, ep, sm_count, st))
-        return rc;
-    }
+  if (dh_bn == 128) {
+    if (int rc = run_dh<kCG, 128>(W, rows, d, V, dH, dz, sm_count, st, res_dh)) return rc;
+  } else {
+    if (int rc = run_dh<kCG, 256>(W, rows, d, V, dH, dz, sm_count, st, res_dh)) return rc;
   }
+  if (!plan.overlap_tail)
+    if (int rc = run_dw<kCG>(H, rows, d, V, dW, dw_dtype, accumulate, dz, sm_count, st, res_dw)) return rc;
   // ---- optional: dbias += column sums of the slab
   if (dbias != nullptr) {
+    ftk::TimelineScope tl_(FTK_TL_DBIAS, st);
     const int rows_per_block = 256;
     dim3 grid(ceil_div(V, 256), ceil_div(rows, rows_per_block));
-    dbias_kernel<<<grid, 128, 0, st>>>(dz, static_cast<int>(rows), V, static_cast<int>(ld), rows_per_block, dbias);
+    dbias_kernel<<<grid, 128, 0, st>>>(dz, static_cast<int>(rows), V, static_cast<int>(dz_pitch(V)), rows_per_block,
+                                       dbias);
     FTK_CUDA_CHECK(cudaGetLastError());
   }
   return FTK_OK;
@@ -1306,6 +1402,7 @@ extern "C" int ftk_lmhead_ce_bwd_kept(const void* H, const void* W, const int64_
   if (dbias != nullptr && !accumulate) FTK_CUDA_CHECK(cudaMemsetAsync(dbias, 0, sizeof(float) * V, st));
   {
     const int n_tiles = ceil_div(V, 256);
+    ftk::TimelineScope tl_(FTK_TL_CONVERT, st);
     probs_to_dz_kernel<<<static_cast<unsigned>(M), 256, n_tiles * sizeof(float), st>>>(
         static_cast<__nv_bfloat16*>(probs), cref, lse, targets, static_cast<int>(M), V, static_cast<int>(ld),
         static_cast<int>(round_up(M, 256)), n_tiles, grad_scale, grad_scale_dev, n_valid_dev);
@@ -1313,9 +1410,201 @@ extern "C" int ftk_lmhead_ce_bwd_kept(const void* H, const void* W, const int64_
   }
   if (cta_group() == 2 && di.sm_count >= 2)
     return run_grad_gemms<2>(H, W, M, d, V, dH, dW, dw_dtype, accumulate, dbias, static_cast<__nv_bfloat16*>(probs),
-                             di.sm_count, st);
+                             di.sm_count, st, GradGemmPlan());
   return run_grad_gemms<1>(H, W, M, d, V, dH, dW, dw_dtype, accumulate, dbias, static_cast<__nv_bfloat16*>(probs),
-                           di.sm_count, st);
+                           di.sm_count, st, GradGemmPlan());
+}
+
+// ------------------------------------------------------------------------------------------------
+// Forward and backward in one call, with a bounded numerators slab (ftk.h: ftk_lmhead_ce_fused).
+namespace {
+
+constexpr size_t kFusedSlabBudget = size_t(1) << 30;  // bytes of bf16 numerators alive at any moment
+
+// Charged time of the forward sweep and the dH GEMM over `r` rows, in 256 x 256 x 64 MMA blocks per SM pair: whole
+// waves over the SM pairs, so a launch that needs 3.46 waves is charged 4.
+int64_t slab_cost(int64_t r, int d, int V, int n_groups, int kCG) {
+  const int n_mblk = ceil_div(r, BM * kCG);
+  int n_chunks, tpc;
+  plan_chunks(n_mblk, ceil_div(V, 256), n_groups, &n_chunks, &tpc);
+  int64_t cost = static_cast<int64_t>(ceil_div(static_cast<int64_t>(n_mblk) * n_chunks, n_groups)) * tpc * (d / 64);
+  const int64_t w256 = ceil_div(static_cast<int64_t>(n_mblk) * ceil_div(d, 256), n_groups) * 2;
+  const int64_t w128 = ceil_div(static_cast<int64_t>(n_mblk) * ceil_div(d, 128), n_groups);
+  const int64_t w = (w128 * kNarrowTilePenaltyPct < w256 * 100) ? (w128 * kNarrowTilePenaltyPct + 99) / 100 : w256;
+  cost += w * ceil_div(V, 64) / 2;
+  return cost;
+}
+
+// Rows per slab: the rows are cut into slabs of R rows plus a remainder, R a multiple of the 256-row tile within the
+// byte budget; R is the value whose forward and dH launches waste the least of their last waves (the dW launches do
+// the same total work whatever the split).  At M = 16,384, d = 2048, 148 SMs: R = 9,472 = 37 row blocks, whose
+// 37 x 8 dH tiles are exactly 4 waves over 74 SM pairs and whose forward is 74 units of half the vocabulary each.
+int64_t plan_fused_slab(int64_t M, int d, int V, int sm_count, int kCG) {
+  const int n_groups = (sm_count > kCG ? sm_count : kCG) / kCG;
+  const int64_t ld = dz_pitch(V);
+  const int64_t step = BM * kCG;
+  int64_t cap = static_cast<int64_t>(kFusedSlabBudget / (static_cast<size_t>(ld) * 2)) / step * step;
+  if (cap < step) cap = step;
+  const int64_t m_pad = round_up(M, step);
+  if (cap > m_pad) cap = m_pad;
+  int64_t best_rows = cap, best_cost = INT64_MAX;
+  for (int64_t rows = cap; rows >= step; rows -= step) {
+    const int64_t n_full = M / rows, rem = M - n_full * rows;
+    if (n_full + (rem > 0) > 256) break;  // ever smaller slabs only add dW read-modify-write passes
+    int64_t cost = n_full * slab_cost(rows, d, V, n_groups, kCG);
+    if (rem > 0) cost += slab_cost(rem, d, V, n_groups, kCG);
+    // each extra slab re-reads and re-writes dW once: about V * d * 8 bytes of HBM traffic, charged as tensor time
+    // at ~100 flop per byte (it overlaps the dW GEMM)
+    cost += (n_full + (rem > 0) - 1) * (static_cast<int64_t>(V) * d * 8 * 100 / (2ll * 256 * 256 * 64)) / n_groups;
+    if (cost < best_cost) {
+      best_cost = cost;
+      best_rows = rows;
+    }
+  }
+  return best_rows;
+}
+
+struct FusedWorkspace {
+  void* fwd;
+  float* cref;
+  __nv_bfloat16* probs;
+  int64_t slab;
+  size_t fwd_bytes, bytes;
+};
+
+FusedWorkspace carve_fused(void* base, int64_t M, int V, int64_t slab) {
+  FusedWorkspace w;
+  if (slab > M) slab = M;
+  w.slab = slab;
+  const uintptr_t p = reinterpret_cast<uintptr_t>(base);
+  size_t off = 0;
+  w.fwd = reinterpret_cast<void*>(p + off);
+  w.fwd_bytes = carve_fwd(nullptr, slab).bytes;
+  off += round_up(w.fwd_bytes, 256);
+  w.cref = reinterpret_cast<float*>(p + off);
+  off += round_up(static_cast<size_t>(ceil_div(V, 256)) * round_up(slab, 256) * sizeof(float), 256);
+  w.probs = reinterpret_cast<__nv_bfloat16*>(p + off);
+  off += static_cast<size_t>(round_up(slab, 256)) * dz_pitch(V) * 2;
+  w.bytes = off;
+  return w;
+}
+
+int fused_slab_rows(int64_t M, int d, int V, int64_t slab_rows, int64_t* out) {
+  ftk::DeviceInfo di;
+  if (int rc = ftk::get_device_info(&di)) return rc;
+  int64_t slab = slab_rows > 0 ? round_up(slab_rows, 256) : plan_fused_slab(M, d, V, di.sm_count, cta_group());
+  if (slab > round_up(M, 256)) slab = round_up(M, 256);
+  *out = slab;
+  return FTK_OK;
+}
+
+}  // namespace
+
+extern "C" int64_t ftk_lmhead_ce_fused_slab_rows(int64_t M, int32_t d, int32_t V, int64_t slab_rows) {
+  int64_t slab = 0;
+  if (M <= 0 || d <= 0 || V <= 0 || fused_slab_rows(M, d, V, slab_rows, &slab)) return 0;
+  return slab;
+}
+
+extern "C" size_t ftk_lmhead_ce_fused_workspace(int64_t M, int32_t d, int32_t V, int64_t slab_rows) {
+  const int64_t slab = ftk_lmhead_ce_fused_slab_rows(M, d, V, slab_rows);
+  if (slab <= 0) return 0;
+  return carve_fused(nullptr, M, V, slab).bytes;
+}
+
+extern "C" int ftk_lmhead_ce_fused(const void* H, const void* W, const void* bias, const int64_t* targets, int64_t M,
+                                   int32_t d, int32_t V, float grad_scale, const float* grad_scale_dev, float* lse,
+                                   float* loss_sum, int32_t* n_valid, void* dH, void* dW, int32_t dw_dtype,
+                                   int32_t accumulate, float* dbias, void* dw_done_event, void* workspace,
+                                   size_t workspace_bytes, int64_t slab_rows, void* stream) {
+  ftk::DeviceInfo di;
+  if (int rc = check_common(H, W, M, d, V, &di)) return rc;
+  FTK_REQUIRE(targets && lse && loss_sum && n_valid && dH && dW && workspace,
+              "ftk_lmhead_ce_fused: null pointer argument");
+  FTK_REQUIRE(dw_dtype == FTK_BF16 || dw_dtype == FTK_F32, "ftk_lmhead_ce_fused: bad dw_dtype %d", dw_dtype);
+  FTK_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "ftk_lmhead_ce_fused: workspace must be 256-byte aligned");
+  FTK_REQUIRE((reinterpret_cast<uintptr_t>(dH) & 15) == 0 && (reinterpret_cast<uintptr_t>(dW) & 15) == 0,
+              "ftk_lmhead_ce_fused: dH/dW must be 16-byte aligned");
+  int64_t slab = 0;
+  if (int rc = fused_slab_rows(M, d, V, slab_rows, &slab)) return rc;
+  const FusedWorkspace fw = carve_fused(workspace, M, V, slab);
+  if (workspace_bytes < fw.bytes)
+    return ftk::fail(FTK_EWORKSPACE, "ftk_lmhead_ce_fused: workspace %zu bytes < required %zu", workspace_bytes,
+                     fw.bytes);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool pair = (cta_group() == 2 && di.sm_count >= 2);
+  // the gradient scale 1 / n_valid is needed by the first slab, before the forward has seen every row: count first
+  FTK_CUDA_CHECK(cudaMemsetAsync(n_valid, 0, sizeof(int32_t), st));
+  FTK_CUDA_CHECK(cudaMemsetAsync(loss_sum, 0, sizeof(float), st));
+  {
+    const int64_t blocks = ceil_div(M, 2048);
+    count_valid_kernel<<<static_cast<unsigned>(blocks < 128 ? blocks : 128), 256, 0, st>>>(targets, M, n_valid);
+    FTK_CUDA_CHECK(cudaGetLastError());
+  }
+  if (dbias != nullptr && !accumulate) FTK_CUDA_CHECK(cudaMemsetAsync(dbias, 0, sizeof(float) * V, st));
+  const int64_t ld = dz_pitch(V);
+  const int n_tiles = ceil_div(V, 256);
+  // Slabs: the remainder (M mod slab rows) first, full slabs after it, so the last slab -- the one whose dH GEMM a
+  // data-parallel caller overlaps with the all-reduce of dW -- is a full one.
+  const int64_t rem = M % fw.slab;
+  bool first = true;
+  for (int64_t r0 = 0; r0 < M;) {
+    const int64_t rows = (r0 == 0 && rem != 0) ? rem : fw.slab;
+    const void* Hs = static_cast<const uint8_t*>(H) + static_cast<size_t>(r0) * d * 2;
+    void* dHs = static_cast<uint8_t*>(dH) + static_cast<size_t>(r0) * d * 2;
+    const FwdWorkspace ws = carve_fwd(fw.fwd, rows);
+    // (1) logits tile by tile: softmax statistics + bf16 numerators of this slab; (2) lse and the slab's loss
+    int rc = pair ? run_fwd_keep<2>(Hs, W, bias, targets + r0, rows, d, V, lse + r0, loss_sum, nullptr, fw.probs,
+                                    fw.cref, ws, di.sm_count, st, 1)
+                  : run_fwd_keep<1>(Hs, W, bias, targets + r0, rows, d, V, lse + r0, loss_sum, nullptr, fw.probs,
+                                    fw.cref, ws, di.sm_count, st, 1);
+    if (rc) return rc;
+    // (3) numerators -> dZ in place
+    {
+      ftk::TimelineScope tl_(FTK_TL_CONVERT, st);
+      probs_to_dz_kernel<<<static_cast<unsigned>(rows), 256, n_tiles * sizeof(float), st>>>(
+          fw.probs, fw.cref, lse + r0, targets + r0, static_cast<int>(rows), V, static_cast<int>(ld),
+          static_cast<int>(round_up(rows, 256)), n_tiles, grad_scale, grad_scale_dev, n_valid);
+      FTK_CUDA_CHECK(cudaGetLastError());
+    }
+    // (4) dH of these rows, dW accumulated over the slabs
+    const int acc = (accumulate || !first) ? 1 : 0;
+    const bool last = r0 + rows >= M;
+    GradGemmPlan plan;
+    plan.overlap_tail = last && dw_done_event != nullptr;
+    plan.full_sms = !plan.overlap_tail;  // the SM reserve only matters where a collective can run beside us
+    plan.dw_done = static_cast<cudaEvent_t>(dw_done_event);
+    rc = pair ? run_grad_gemms<2>(Hs, W, rows, d, V, dHs, dW, dw_dtype, acc, dbias, fw.probs, di.sm_count, st, plan)
+              : run_grad_gemms<1>(Hs, W, rows, d, V, dHs, dW, dw_dtype, acc, dbias, fw.probs, di.sm_count, st, plan);
+    if (rc) return rc;
+    r0 += rows;
+    first = false;
+  }
+  return FTK_OK;
+}
+
+extern "C" int ftk_scale_unless_one(void* buf, size_t n, int32_t dtype, const float* factor_dev, int32_t poison,
+                                    void* stream) {
+  FTK_REQUIRE(buf && factor_dev, "ftk_scale_unless_one: null pointer argument");
+  FTK_REQUIRE(dtype == FTK_BF16 || dtype == FTK_F32, "ftk_scale_unless_one: bad dtype %d", dtype);
+  const size_t per_vec = dtype == FTK_F32 ? 4 : 8;
+  FTK_REQUIRE(n % per_vec == 0 && (reinterpret_cast<uintptr_t>(buf) & 15) == 0,
+              "ftk_scale_unless_one: buffer must be 16-byte aligned and hold a multiple of %zu elements", per_vec);
+  if (n == 0) return FTK_OK;
+  ftk::DeviceInfo di;
+  if (int rc = ftk::get_device_info(&di)) return rc;
+  const size_t n_vec = n / per_vec;
+  size_t blocks = (n_vec + 255) / 256;
+  if (blocks > static_cast<size_t>(di.sm_count) * 8) blocks = static_cast<size_t>(di.sm_count) * 8;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == FTK_F32)
+    scale_unless_one_kernel<float><<<static_cast<unsigned>(blocks), 256, 0, st>>>(static_cast<float*>(buf), n_vec, factor_dev,
+                                                                                  poison);
+  else
+    scale_unless_one_kernel<__nv_bfloat16><<<static_cast<unsigned>(blocks), 256, 0, st>>>(
+        static_cast<__nv_bfloat16*>(buf), n_vec, factor_dev, poison);
+  FTK_CUDA_CHECK(cudaGetLastError());
+  return FTK_OK;
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -137,9 +137,12 @@ __global__ void __launch_bounds__(kThreads) adamw_f32_kernel(float* __restrict__
   }
 }
 
-// bf16 parameters with an fp32 master copy: the master is updated, the bf16 parameter is its rounding
+// bf16 parameters with an fp32 master copy: the master is updated, the bf16 parameter is its rounding.
+// The gradient is bf16, or fp32 (main gradients accumulated and all-reduced in fp32, as the reference's
+// ds_config.json:45 "communication_data_type": "fp32" and DeepSpeed's fp32 gradient accumulation do).
+template <typename GT>
 __global__ void __launch_bounds__(kThreads) adamw_bf16_kernel(__nv_bfloat16* __restrict__ p,
-                                                              const __nv_bfloat16* __restrict__ g,
+                                                              const GT* __restrict__ g,
                                                               float* __restrict__ master, float* __restrict__ m,
                                                               float* __restrict__ v, size_t n, AdamArgs a) {
   const float gs = a.gscale * (a.gscale_dev != nullptr ? __ldg(a.gscale_dev) : 1.f);
@@ -147,19 +150,25 @@ __global__ void __launch_bounds__(kThreads) adamw_bf16_kernel(__nv_bfloat16* __r
   for (size_t i = blockIdx.x * static_cast<size_t>(kThreads) + threadIdx.x; i < n8;
        i += static_cast<size_t>(gridDim.x) * kThreads) {
     // optimizer state is touched once per step: streaming loads and stores keep it from displacing anything in L2
-    const uint4 gv = __ldcs(reinterpret_cast<const uint4*>(g) + i);
-    const uint32_t gw[4] = {gv.x, gv.y, gv.z, gv.w};
+    float gg[8];
+    if constexpr (sizeof(GT) == 4) {
+      const float4 g0 = __ldcs(reinterpret_cast<const float4*>(g) + 2 * i);
+      const float4 g1 = __ldcs(reinterpret_cast<const float4*>(g) + 2 * i + 1);
+      gg[0] = g0.x, gg[1] = g0.y, gg[2] = g0.z, gg[3] = g0.w, gg[4] = g1.x, gg[5] = g1.y, gg[6] = g1.z, gg[7] = g1.w;
+    } else {
+      const uint4 gv = __ldcs(reinterpret_cast<const uint4*>(g) + i);
+      const uint32_t gw[4] = {gv.x, gv.y, gv.z, gv.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&gw[e]);
+        gg[2 * e] = __low2float(h);
+        gg[2 * e + 1] = __high2float(h);
+      }
+    }
     float4 w0 = __ldcs(reinterpret_cast<const float4*>(master) + 2 * i);
     float4 w1 = __ldcs(reinterpret_cast<const float4*>(master) + 2 * i + 1);
     float4 m0 = __ldcs(reinterpret_cast<const float4*>(m) + 2 * i), m1 = __ldcs(reinterpret_cast<const float4*>(m) + 2 * i + 1);
     float4 v0 = __ldcs(reinterpret_cast<const float4*>(v) + 2 * i), v1 = __ldcs(reinterpret_cast<const float4*>(v) + 2 * i + 1);
-    float gg[8];
-#pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&gw[e]);
-      gg[2 * e] = __low2float(h);
-      gg[2 * e + 1] = __high2float(h);
-    }
     w0.x = adamw_one(w0.x, gg[0], m0.x, v0.x, a, gs);
     w0.y = adamw_one(w0.y, gg[1], m0.y, v0.y, a, gs);
     w0.z = adamw_one(w0.z, gg[2], m0.z, v0.z, a, gs);
@@ -188,7 +197,7 @@ __global__ void __launch_bounds__(kThreads) adamw_bf16_kernel(__nv_bfloat16* __r
   }
   if (blockIdx.x == 0 && threadIdx.x < n - n8 * 8) {
     const size_t i = n8 * 8 + threadIdx.x;
-    master[i] = adamw_one(master[i], __bfloat162float(g[i]), m[i], v[i], a, gs);
+    master[i] = adamw_one(master[i], static_cast<float>(g[i]), m[i], v[i], a, gs);
     p[i] = __float2bfloat16(master[i]);
   }
 }
@@ -220,6 +229,7 @@ extern "C" int ftk_grad_sqnorm(const void* grad, size_t n, int32_t dtype, float*
   float* partial = static_cast<float*>(workspace);
   unsigned int* ticket = reinterpret_cast<unsigned int*>(static_cast<uint8_t*>(workspace) + sizeof(float) * kMaxBlocks);
   FTK_CUDA_CHECK(cudaMemsetAsync(ticket, 0, sizeof(unsigned int), st));
+  ftk::TimelineScope tl_(FTK_TL_SQNORM, st);
   if (dtype == FTK_F32)
     sqnorm_kernel<float><<<grid_for(n / 4, di.sm_count), kThreads, 0, st>>>(static_cast<const float*>(grad), n, partial,
                                                                           ticket, out, accumulate);
@@ -244,8 +254,8 @@ extern "C" int ftk_adamw_step(void* param, const void* grad, float* master, floa
                               void* stream) {
   FTK_REQUIRE(param && grad && exp_avg && exp_avg_sq, "ftk_adamw_step: null pointer argument");
   FTK_REQUIRE(step >= 1, "ftk_adamw_step: step counts from 1");
-  FTK_REQUIRE(param_dtype == FTK_F32 || (param_dtype == FTK_BF16 && grad_dtype == FTK_BF16 && master != nullptr),
-              "ftk_adamw_step: bf16 parameters need bf16 gradients and an fp32 master copy");
+  FTK_REQUIRE(param_dtype == FTK_F32 || (param_dtype == FTK_BF16 && master != nullptr),
+              "ftk_adamw_step: bf16 parameters need an fp32 master copy");
   FTK_REQUIRE(grad_dtype == FTK_F32 || grad_dtype == FTK_BF16, "ftk_adamw_step: bad grad dtype %d", grad_dtype);
   const uintptr_t al = reinterpret_cast<uintptr_t>(param) | reinterpret_cast<uintptr_t>(grad) |
                        reinterpret_cast<uintptr_t>(exp_avg) | reinterpret_cast<uintptr_t>(exp_avg_sq) |
@@ -265,6 +275,7 @@ extern "C" int ftk_adamw_step(void* param, const void* grad, float* master, floa
   a.gscale = grad_scale;
   a.gscale_dev = grad_scale_dev;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  ftk::TimelineScope tl_(FTK_TL_ADAMW, st);
   if (param_dtype == FTK_F32) {
     if (grad_dtype == FTK_F32)
       adamw_f32_kernel<float><<<grid_for(n / 4, di.sm_count), kThreads, 0, st>>>(
@@ -272,8 +283,11 @@ extern "C" int ftk_adamw_step(void* param, const void* grad, float* master, floa
     else
       adamw_f32_kernel<__nv_bfloat16><<<grid_for(n / 4, di.sm_count), kThreads, 0, st>>>(
           static_cast<float*>(param), static_cast<const __nv_bfloat16*>(grad), exp_avg, exp_avg_sq, n, a);
+  } else if (grad_dtype == FTK_F32) {
+    adamw_bf16_kernel<float><<<grid_for(n / 8, di.sm_count), kThreads, 0, st>>>(
+        static_cast<__nv_bfloat16*>(param), static_cast<const float*>(grad), master, exp_avg, exp_avg_sq, n, a);
   } else {
-    adamw_bf16_kernel<<<grid_for(n / 8, di.sm_count), kThreads, 0, st>>>(
+    adamw_bf16_kernel<__nv_bfloat16><<<grid_for(n / 8, di.sm_count), kThreads, 0, st>>>(
         static_cast<__nv_bfloat16*>(param), static_cast<const __nv_bfloat16*>(grad), master, exp_avg, exp_avg_sq, n, a);
   }
   FTK_CUDA_CHECK(cudaGetLastError());

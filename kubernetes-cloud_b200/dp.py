@@ -6,6 +6,14 @@ filled in reverse parameter order as backward runs, and a full bucket is all-red
 communication stream while backward continues.  Under gradient accumulation only the last micro-batch reduces.
 Plain DP: every rank holds a full replica (no ZeRO partitioning).
 
+Gradient precision.  The reference reduces in fp32 (ds_config.json:45 ``"communication_data_type": "fp32"``) and
+DeepSpeed accumulates micro-batch gradients of 16-bit parameters in fp32.  ``main_grads=True`` (the default whenever
+a parameter is bf16) does the same: every bucket is an fp32 buffer, each parameter gets a ``main_grad`` view of it,
+the bf16 ``param.grad`` autograd produces for a micro-batch is added into ``main_grad`` by the grad-ready hook and
+dropped, the fused lm_head loss adds its weight gradient into ``main_grad`` straight from the dW GEMM, and the
+all-reduce and the optimizer consume the fp32 buckets.  ``main_grads=False`` keeps gradients, accumulation and the wire
+in the parameter dtype (half the NVLink bytes, bf16 rounding on every add).
+
 Backends
   "ftk"   the C ABI's NCCL communicator (ftk_dp_*): one ncclAllReduce per bucket on a high-priority stream over
           NVLink/NVSwitch, pre-scaled by 1/world.  GPU only.
@@ -33,11 +41,17 @@ class _Bucket:
 
 class GradSync:
     def __init__(self, params: Iterable[torch.nn.Parameter], rank: int, world: int, bucket_bytes: int = 128 << 20,
-                 backend: str = "ftk", grad_dtype: Optional[torch.dtype] = None, average: bool = True):
+                 backend: str = "ftk", grad_dtype: Optional[torch.dtype] = None, average: bool = True,
+                 main_grads: Optional[bool] = None):
         self.rank, self.world, self.backend, self.average = rank, world, backend, average
         self.params = [p for p in params if p.requires_grad]
         if not self.params:
             raise ValueError("no trainable parameters")
+        if main_grads is None:
+            main_grads = grad_dtype is None and any(p.dtype == torch.bfloat16 for p in self.params)
+        self.main_grads = bool(main_grads)
+        if self.main_grads:
+            grad_dtype = torch.float32
         self.device = self.params[0].device
         if backend == "ftk" and self.device.type != "cuda":
             raise _lib.FtkError('backend "ftk" needs CUDA parameters (use "gloo" only for CPU tests)')
@@ -68,7 +82,12 @@ class GradSync:
             flat = torch.zeros(n, dtype=dt, device=self.device)
             off = 0
             for p in g:
-                p.grad = flat[off:off + p.numel()].view_as(p)
+                view = flat[off:off + p.numel()].view_as(p)
+                if self.main_grads:
+                    p.main_grad = view  # the fused lm_head loss looks for this attribute (ops._wgrad_target)
+                    p.grad = None
+                else:
+                    p.grad = view
                 off += (p.numel() + 7) // 8 * 8
             b = _Bucket(flat, g)
             self.buckets.append(b)
@@ -100,6 +119,9 @@ class GradSync:
 
     # ------------------------------------------------------------------ hooks
     def _on_ready(self, p: torch.nn.Parameter) -> None:
+        if self.main_grads and p.grad is not None:
+            p.main_grad.add_(p.grad)  # bf16 micro-batch gradient into the fp32 main gradient
+            p.grad = None
         if not self.sync_now:
             return
         b = self._bucket_of[p]
@@ -107,7 +129,20 @@ class GradSync:
         if b.pending == 0:
             self._launch(b)
 
-    def _launch(self, b: _Bucket) -> None:
+    def mark_ready(self, p: torch.nn.Parameter, after: Optional[torch.cuda.Event] = None) -> None:
+        """Tell the sync that ``p``'s gradient is final although no autograd hook will fire for it: the fused lm_head
+        loss writes an untied ``lm_head.weight`` gradient into ``main_grad`` (or ``grad``) itself.  If that completes
+        ``p``'s bucket, its all-reduce is launched now, and with ``after`` (the event given to
+        ``ops.set_dw_done_event``) it waits for that event only, not for what the compute stream was given since:
+        the transfer then runs beside the dH GEMM.  Ignored inside ``no_sync()``."""
+        if not self.sync_now:
+            return
+        b = self._bucket_of[p]
+        b.pending -= 1
+        if b.pending == 0:
+            self._launch(b, after)
+
+    def _launch(self, b: _Bucket, after: Optional[torch.cuda.Event] = None) -> None:
         scale = (1.0 / self.world) if self.average else 1.0
         self.launched += 1
         if self.backend == "ftk":
@@ -116,8 +151,13 @@ class GradSync:
                 raise _lib.FtkError(f"unsupported gradient dtype {b.flat.dtype}")
             stream = torch.cuda.current_stream(self.device).cuda_stream
             with torch.cuda.device(self.device):
-                _lib.check(_lib.lib().ftk_dp_allreduce(self._handle, b.flat.data_ptr(), b.flat.numel(), dt, scale,
-                                                       stream), "ftk_dp_allreduce")
+                if after is not None:
+                    _lib.check(_lib.lib().ftk_dp_allreduce_after(self._handle, b.flat.data_ptr(), b.flat.numel(), dt,
+                                                                 scale, int(after.cuda_event)),
+                               "ftk_dp_allreduce_after")
+                else:
+                    _lib.check(_lib.lib().ftk_dp_allreduce(self._handle, b.flat.data_ptr(), b.flat.numel(), dt, scale,
+                                                           stream), "ftk_dp_allreduce")
         else:
             if scale != 1.0:
                 b.flat.mul_(scale)
@@ -133,11 +173,12 @@ class GradSync:
         finally:
             self.sync_now = old
 
-    def finish(self) -> None:
+    def finish(self, reduce: bool = True) -> None:
         """Call after the last backward of an optimizer step: reduces any bucket whose hooks did not all fire
-        (parameters without gradient this step) and makes the current stream wait for the communication stream."""
+        (parameters without gradient this step) and makes the current stream wait for the communication stream.
+        ``reduce=False`` only re-arms the buckets (a step measured without its communication)."""
         for b in self.buckets:
-            if b.pending != 0:
+            if b.pending != 0 and reduce:
                 self._launch(b)
         if self.backend == "ftk":
             stream = torch.cuda.current_stream(self.device).cuda_stream

@@ -168,9 +168,11 @@ def main(argv: Optional[List[str]] = None) -> dict:
                 last = g == args.gradients - 1
                 ctx = sync.no_sync() if not last else _null()
                 with ctx:
-                    loss = compute_loss(model, batch, labels_are_shifted=True)
-                    (loss / args.gradients).backward()  # HF Trainer scales by 1/GAS before backward
-                losses.append(loss.detach())
+                    # HF Trainer scales the loss by 1/GAS before backward; here the factor goes into the fused loss,
+                    # whose gradients are made during the forward call
+                    loss = compute_loss(model, batch, labels_are_shifted=True, loss_scale=1.0 / args.gradients)
+                    loss.backward()
+                losses.append(loss.detach() * args.gradients)
             sync.finish()
             lr_used = opt.current_lr()
             opt.step()

@@ -30,8 +30,10 @@ def _trunk_and_head(model):
 
 
 def compute_loss(model, inputs: dict, return_outputs: bool = False, num_items_in_batch=None,
-                 labels_are_shifted: bool = False):
-    """Same signature and meaning as the reference's override (plus the keyword newer Trainers pass)."""
+                 labels_are_shifted: bool = False, loss_scale: float = 1.0):
+    """Same signature and meaning as the reference's override (plus the keyword newer Trainers pass).
+    ``loss_scale``: returns ``loss_scale * loss``; a loop that accumulates gradients passes 1 / accumulation steps
+    here and calls ``.backward()`` on the result directly (see ``ops.fused_lmhead_ce``)."""
     labels = inputs.get("labels")
     if labels is not None and not labels_are_shifted:
         labels.masked_fill_(~inputs["attention_mask"], IGNORE)  # FT.py:476-477, in place like the reference
@@ -46,7 +48,7 @@ def compute_loss(model, inputs: dict, return_outputs: bool = False, num_items_in
     b = getattr(head, "bias", None)
     if b is not None and b.dtype != torch.bfloat16:
         b = b.to(torch.bfloat16)
-    loss = fused_lmhead_ce(h2.contiguous(), w.contiguous(), b, targets.reshape(-1).contiguous())
+    loss = fused_lmhead_ce(h2.contiguous(), w.contiguous(), b, targets.reshape(-1).contiguous(), loss_scale)
     if not loss.requires_grad:
         loss.requires_grad_(True)  # FT.py:483
     return (loss, {"loss": loss, "hidden_states": hidden}) if return_outputs else loss

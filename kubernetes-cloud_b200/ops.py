@@ -281,19 +281,122 @@ def _(H, W, has_bias, targets, lse, probs, cref, grad_out, n_valid, grad_scale, 
     return torch.empty_like(H), H.new_empty((W.shape[0] if has_bias else 0,), dtype=torch.float32)
 
 
-_backward_mode = "recompute"
+_fused_slab_rows = 0  # 0 = the library's choice; tests shrink it to exercise several slabs
+
+
+def set_fused_slab_rows(rows: int) -> None:
+    global _fused_slab_rows
+    _fused_slab_rows = int(rows)
+
+
+def _fused_impl(H, W, bias, targets, grad_scale, dw_fp32, dw_event, dW_into):
+    global _launches
+    _check_hw(H, W, bias, targets)
+    M, d = H.shape
+    V = W.shape[0]
+    dev = H.device
+    L = _lib.lib()
+    lse = torch.empty((M,), dtype=torch.float32, device=dev)
+    loss_sum = torch.empty((1,), dtype=torch.float32, device=dev)
+    n_valid = torch.empty((1,), dtype=torch.int32, device=dev)
+    dH = torch.empty((M, d), dtype=torch.bfloat16, device=dev)
+    dW, dw_code, acc = _dw_target(W, dw_fp32, dW_into)
+    dbias = torch.empty((V if bias is not None else 0,), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        ws_bytes = L.ftk_lmhead_ce_fused_workspace(M, d, V, _fused_slab_rows)
+        slab = L.ftk_lmhead_ce_fused_slab_rows(M, d, V, _fused_slab_rows)
+        ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=dev)
+        rc = L.ftk_lmhead_ce_fused(H.data_ptr(), W.data_ptr(), _ptr(bias), targets.data_ptr(), M, d, V, grad_scale, 0,
+                                   lse.data_ptr(), loss_sum.data_ptr(), n_valid.data_ptr(), dH.data_ptr(),
+                                   dW.data_ptr(), dw_code, acc, dbias.data_ptr() if bias is not None else 0,
+                                   int(dw_event), ws.data_ptr(), ws_bytes, _fused_slab_rows, _stream(H))
+    _lib.check(rc, "ftk_lmhead_ce_fused")
+    n_slabs = (M + slab - 1) // slab
+    _launches += 1 + n_slabs * (5 + (1 if bias is not None else 0))  # count; per slab: sweep, finalize, dZ, dH, dW
+    return loss_sum, n_valid, lse, dH, dW, dbias
+
+
+@torch.library.custom_op("ftk::lmhead_ce_fused", mutates_args=())
+def lmhead_ce_fused(H: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor], targets: torch.Tensor,
+                    grad_scale: float, dw_fp32: bool, dw_event: int
+                    ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
+    """Forward and backward in one call (ftk_lmhead_ce_fused): returns (loss_sum, n_valid, lse, dH, dW, dbias) with
+    the gradients of ``grad_scale * mean loss``.  ``dw_event``: 0, or the handle of a CUDA event to record once dW
+    is complete (the last slab then computes dW before dH)."""
+    return _fused_impl(H, W, bias, targets, grad_scale, dw_fp32, dw_event, None)
+
+
+@lmhead_ce_fused.register_fake
+def _(H, W, bias, targets, grad_scale, dw_fp32, dw_event):
+    return (H.new_empty((1,), dtype=torch.float32), H.new_empty((1,), dtype=torch.int32),
+            H.new_empty((H.shape[0],), dtype=torch.float32), torch.empty_like(H),
+            W.new_empty(W.shape, dtype=torch.float32 if dw_fp32 else torch.bfloat16),
+            H.new_empty((W.shape[0] if bias is not None else 0,), dtype=torch.float32))
+
+
+@torch.library.custom_op("ftk::lmhead_ce_fused_into", mutates_args=("dW_into",))
+def lmhead_ce_fused_into(H: torch.Tensor, W: torch.Tensor, bias: Optional[torch.Tensor], targets: torch.Tensor,
+                         grad_scale: float, dw_event: int, dW_into: torch.Tensor
+                         ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
+    """``lmhead_ce_fused`` with the dW GEMM adding into ``dW_into``.  Returns (loss_sum, n_valid, lse, dH, dbias)."""
+    loss_sum, n_valid, lse, dH, _, dbias = _fused_impl(H, W, bias, targets, grad_scale, False, dw_event, dW_into)
+    return loss_sum, n_valid, lse, dH, dbias
+
+
+@lmhead_ce_fused_into.register_fake
+def _(H, W, bias, targets, grad_scale, dw_event, dW_into):
+    return (H.new_empty((1,), dtype=torch.float32), H.new_empty((1,), dtype=torch.int32),
+            H.new_empty((H.shape[0],), dtype=torch.float32), torch.empty_like(H),
+            H.new_empty((W.shape[0] if bias is not None else 0,), dtype=torch.float32))
+
+
+def _scale_unless_one(t: torch.Tensor, factor: torch.Tensor, poison: bool = False) -> None:
+    """t *= factor (a device scalar) unless factor == 1, decided on the device: no host synchronisation."""
+    global _launches
+    if t.numel() == 0:
+        return
+    code = _lib.FTK_F32 if t.dtype == torch.float32 else _lib.FTK_BF16
+    per = 4 if t.dtype == torch.float32 else 8
+    flat = t.view(-1)
+    n = flat.numel() // per * per
+    with torch.cuda.device(t.device):
+        _lib.check(_lib.lib().ftk_scale_unless_one(flat.data_ptr(), n, code, factor.data_ptr(), int(poison), _stream(t)),
+                   "ftk_scale_unless_one")
+    _launches += 1
+    if n != flat.numel():  # a tail shorter than one 16-byte vector (odd vocabulary sizes of dbias)
+        flat[n:].mul_(torch.where(factor == 1, factor, factor * (float("nan") if poison else 1.0)))
+
+
+_backward_mode = "fused"
 _keep_budget_bytes = 8 << 30
+_dw_done_event: Optional[torch.cuda.Event] = None
 
 
 def set_backward_mode(mode: str, keep_budget_bytes: int = 8 << 30) -> None:
-    """"recompute" (default): nothing of size [tokens, vocab] survives the forward; the backward recomputes the
-    logits tile by tile.  "keep": the forward also stores the bf16 softmax numerators (tokens x vocab x 2 bytes, used
-    only while they fit ``keep_budget_bytes``), and the backward skips the recompute GEMM -- about a quarter less
-    tensor work per training step."""
+    """How ``fused_lmhead_ce`` obtains its gradients.
+    "fused" (default): when both hidden and weight need gradients, the forward call computes them as well
+    (ftk_lmhead_ce_fused), slab by slab, so the logits are formed once and nothing of size [tokens, vocab] outlives a
+    slab; ``backward`` only rescales by the upstream gradient.  dH and dW exist from forward to backward.
+    "recompute": forward keeps only lse; the backward recomputes the logits tile by tile (a third more tensor work).
+    "keep": the forward stores ALL bf16 softmax numerators (tokens x vocab x 2 bytes, used only while they fit
+    ``keep_budget_bytes``) and the backward skips the recompute GEMM."""
     global _backward_mode, _keep_budget_bytes
-    if mode not in ("recompute", "keep"):
+    if mode not in ("fused", "recompute", "keep"):
         raise ValueError(mode)
     _backward_mode, _keep_budget_bytes = mode, int(keep_budget_bytes)
+
+
+def set_dw_done_event(event: Optional[torch.cuda.Event]) -> None:
+    """Data-parallel callers ("fused" mode): an event ``fused_lmhead_ce`` records as soon as the weight gradient is
+    complete.  With one set, the last slab computes dW before dH and runs that dH GEMM on the SMs the
+    ``sm_reserve`` option leaves to others, so an all-reduce waiting on the event (``GradSync.mark_ready``) overlaps
+    it.  None switches this off.  The event must have been recorded once already (its handle exists only then)."""
+    global _dw_done_event
+    _dw_done_event = event
+
+
+def _dw_event_handle() -> int:
+    return 0 if _dw_done_event is None else int(_dw_done_event.cuda_event)
 
 
 def _wgrad_target(weight: torch.Tensor) -> Optional[torch.Tensor]:
@@ -317,51 +420,92 @@ def _wgrad_target(weight: torch.Tensor) -> Optional[torch.Tensor]:
 
 class _FusedLmHeadCE(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, hidden, weight, bias, targets):
+    def forward(ctx, hidden, weight, bias, targets, loss_scale):
         M, V = hidden.shape[0], weight.shape[0]
-        keep = (_backward_mode == "keep" and torch.is_grad_enabled()
-                and _lib.lib().ftk_lmhead_ce_probs_bytes(M, V) <= _keep_budget_bytes)
-        ctx.keep = keep
-        if keep:
+        want_h, want_w = ctx.needs_input_grad[0], ctx.needs_input_grad[1]  # grad mode is off inside forward
+        ctx.mode = "none"
+        ctx.loss_scale = float(loss_scale)
+        ctx.consumed = False
+        if _backward_mode == "fused" and want_h and want_w:
+            ctx.mode = "fused"
+            into = _wgrad_target(weight)
+            if into is not None:
+                loss_sum, n_valid, lse, dH, dbias = torch.ops.ftk.lmhead_ce_fused_into(hidden, weight, bias, targets,
+                                                                                       ctx.loss_scale, _dw_event_handle(), into)
+                dW = None
+            else:
+                loss_sum, n_valid, lse, dH, dW, dbias = torch.ops.ftk.lmhead_ce_fused(hidden, weight, bias, targets,
+                                                                                      ctx.loss_scale, False, _dw_event_handle())
+            ctx.grads = (dH, dW, dbias if bias is not None else None, into is not None)
+            ctx.bias_dtype = bias.dtype if bias is not None else None
+        elif (_backward_mode == "keep" and (want_h or want_w)
+              and _lib.lib().ftk_lmhead_ce_probs_bytes(M, V) <= _keep_budget_bytes):
+            ctx.mode = "keep"
             loss_sum, n_valid, lse, probs, cref = torch.ops.ftk.lmhead_ce_fwd_keep(hidden, weight, bias, targets)
             ctx.save_for_backward(hidden, weight, bias, targets, lse, n_valid, probs, cref)
         else:
+            if want_h or want_w:
+                ctx.mode = "recompute"
             loss_sum, n_valid, lse = torch.ops.ftk.lmhead_ce_fwd(hidden, weight, bias, targets)
             ctx.save_for_backward(hidden, weight, bias, targets, lse, n_valid)
-        ctx.consumed = False
         # mean over valid rows (transformers fixed_cross_entropy, reduction="mean"); 0/0 -> NaN as in the reference
-        return (loss_sum / n_valid.to(torch.float32)).reshape(())
+        loss = (loss_sum / n_valid.to(torch.float32)).reshape(())
+        return loss * ctx.loss_scale if ctx.loss_scale != 1.0 else loss
 
     @staticmethod
     def backward(ctx, grad_out):
+        if ctx.consumed:
+            raise _lib.FtkError("fused_lmhead_ce: this loss was already backpropagated (gradients / kept numerators "
+                                "are consumed by the first backward; use set_backward_mode('recompute') to do it twice)")
+        go = grad_out.reshape(1).to(torch.float32)
+        if ctx.mode == "fused":
+            # the gradients of loss_scale * mean-loss exist already; all that is left is the upstream factor, which
+            # is 1 for ``loss.backward()`` -- checked on the device, so the common case costs three empty launches
+            dH, dW, dbias, accumulated = ctx.grads
+            ctx.grads = None
+            ctx.consumed = True
+            if accumulated:
+                # dW already sits inside the caller's gradient buffer and cannot be rescaled on its own: make a wrong
+                # assumption visible (NaN in dH) rather than return a silently mis-scaled weight gradient
+                _scale_unless_one(dH, go, poison=True)
+            else:
+                _scale_unless_one(dH, go)
+                _scale_unless_one(dW, go)
+            if dbias is not None:
+                _scale_unless_one(dbias, go)
+            return dH, dW, (dbias.to(ctx.bias_dtype) if dbias is not None else None), None, None
         weight = ctx.saved_tensors[1]
         into = _wgrad_target(weight) if ctx.needs_input_grad[1] else None
-        go = grad_out.reshape(1)
         dW = None
-        if ctx.keep:
-            if ctx.consumed:
-                raise _lib.FtkError("the kept softmax numerators were consumed by the first backward "
-                                    "(use set_backward_mode('recompute') to backpropagate twice)")
+        if ctx.mode == "keep":
             hidden, weight, bias, targets, lse, n_valid, probs, cref = ctx.saved_tensors
             if into is not None:
                 dH, dbias = torch.ops.ftk.lmhead_ce_bwd_kept_into(hidden, weight, bias is not None, targets, lse, probs,
-                                                                  cref, go, n_valid, 1.0, into)
+                                                                  cref, go, n_valid, ctx.loss_scale, into)
             else:
                 dH, dW, dbias = torch.ops.ftk.lmhead_ce_bwd_kept(hidden, weight, bias is not None, targets, lse, probs,
-                                                                 cref, go, n_valid, 1.0, False)
+                                                                 cref, go, n_valid, ctx.loss_scale, False)
             ctx.consumed = True
         else:
             hidden, weight, bias, targets, lse, n_valid = ctx.saved_tensors
             if into is not None:
-                dH, dbias = torch.ops.ftk.lmhead_ce_bwd_into(hidden, weight, bias, targets, lse, go, n_valid, 1.0, into)
+                dH, dbias = torch.ops.ftk.lmhead_ce_bwd_into(hidden, weight, bias, targets, lse, go, n_valid,
+                                                             ctx.loss_scale, into)
             else:
-                dH, dW, dbias = torch.ops.ftk.lmhead_ce_bwd(hidden, weight, bias, targets, lse, go, n_valid, 1.0, False)
-        return dH, dW, (dbias.to(bias.dtype) if bias is not None else None), None
+                dH, dW, dbias = torch.ops.ftk.lmhead_ce_bwd(hidden, weight, bias, targets, lse, go, n_valid,
+                                                            ctx.loss_scale, False)
+        return dH, dW, (dbias.to(bias.dtype) if bias is not None else None), None, None
 
 
 def fused_lmhead_ce(hidden: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor],
-                    targets: torch.Tensor) -> torch.Tensor:
-    """Mean causal-LM cross-entropy of logits = hidden @ weight.T (+ bias) against already shifted targets
-    (-100 = ignore).  hidden [M,d] bf16, weight [V,d] bf16.  Differentiable; the logits never reach HBM
-    (see ``set_backward_mode`` for the opt-in mode that keeps bf16 softmax numerators instead of recomputing)."""
-    return _FusedLmHeadCE.apply(hidden, weight, bias, targets)
+                    targets: torch.Tensor, loss_scale: float = 1.0) -> torch.Tensor:
+    """``loss_scale`` x mean causal-LM cross-entropy of logits = hidden @ weight.T (+ bias) against already shifted
+    targets (-100 = ignore).  hidden [M,d] bf16, weight [V,d] bf16.  Differentiable; the full logits never reach HBM
+    (``set_backward_mode`` describes the three ways the gradients are obtained).
+
+    ``loss_scale`` is where a training loop puts its 1 / gradient_accumulation_steps: in the default mode the
+    gradients are produced during this call, already carrying that factor, and ``loss.backward()`` then finds an
+    upstream gradient of exactly 1 and has nothing left to do.  Any other upstream gradient is still honoured by a
+    rescaling pass, except for a weight gradient that was accumulated straight into ``weight.main_grad`` /
+    ``weight.grad``: there it poisons dH with NaN instead of returning a wrong result."""
+    return _FusedLmHeadCE.apply(hidden, weight, bias, targets, loss_scale)

@@ -58,8 +58,9 @@ class FusedAdamW:
             pdt = b.params[0].dtype
             if pdt not in (torch.float32, torch.bfloat16) or any(p.dtype != pdt for p in b.params):
                 raise _lib.FtkError("parameters of a bucket must all be fp32 or all bf16")
-            if pdt == torch.bfloat16 and b.flat.dtype != torch.bfloat16:
-                raise _lib.FtkError("bf16 parameters need bf16 gradient buckets")
+            if b.flat.dtype not in (torch.float32, torch.bfloat16) or (pdt == torch.float32
+                                                                        and b.flat.dtype != torch.float32):
+                raise _lib.FtkError("gradient buckets must be fp32, or bf16 for bf16 parameters")
             flat = torch.zeros(n, dtype=pdt, device=dev)
             off = 0
             for p in b.params:  # same packing as GradSync: 8-element aligned views

@@ -5,12 +5,16 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-def test_grad_sync_ftk_world1_prescale_and_overlap_stream(cuda_dev):
+@pytest.mark.parametrize("main_grads", [True, False])
+def test_grad_sync_ftk_world1_prescale_and_overlap_stream(cuda_dev, main_grads):
+    """bf16 parameters; fp32 main gradients (the default, as the reference reduces in fp32) and bf16 buckets."""
     from kubernetes_cloud_b200.dp import GradSync
     torch.manual_seed(0)
     model = torch.nn.Sequential(torch.nn.Linear(64, 128), torch.nn.GELU(), torch.nn.Linear(128, 64)).cuda().to(torch.bfloat16)
     ref = [p.detach().clone().float().requires_grad_(True) for p in model.parameters()]
-    sync = GradSync(model.parameters(), 0, 1, bucket_bytes=16 << 10, backend="ftk", average=True)
+    sync = GradSync(model.parameters(), 0, 1, bucket_bytes=16 << 10, backend="ftk", average=True,
+                    main_grads=main_grads)
+    assert sync.main_grads == main_grads
     x = torch.randn(32, 64, device="cuda", dtype=torch.bfloat16)
     sync.zero_grad()
     with sync.no_sync():
@@ -28,7 +32,10 @@ def test_grad_sync_ftk_world1_prescale_and_overlap_stream(cuda_dev):
     for _ in range(2):
         model2(x).float().pow(2).mean().backward()
     for p, q in zip(model.parameters(), model2.parameters()):
-        assert torch.allclose(p.grad.float(), q.grad.float(), rtol=2e-2, atol=1e-4)
+        got = p.main_grad if main_grads else p.grad
+        assert got.dtype == (torch.float32 if main_grads else torch.bfloat16)
+        assert torch.allclose(got.float(), q.grad.float(), rtol=2e-2, atol=1e-4)
+        assert (p.grad is None) == main_grads
     sync.close()
 
 

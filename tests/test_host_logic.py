@@ -92,6 +92,55 @@ def test_grad_sync_gloo_world2():
             assert out[r] < 1e-6
 
 
+def _worker_main_grads(rank, world, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from kubernetes_cloud_b200.dp import GradSync
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(16, 32), torch.nn.Tanh(), torch.nn.Linear(32, 8)).to(torch.bfloat16)
+    sync = GradSync(model.parameters(), rank, world, bucket_bytes=2048, backend="gloo")
+    assert sync.main_grads and all(b.flat.dtype == torch.float32 for b in sync.buckets)
+    g = torch.Generator().manual_seed(200 + rank)
+    xs = [torch.randn(4, 16, generator=g).to(torch.bfloat16) for _ in range(3)]
+    sync.zero_grad()
+    with sync.no_sync():
+        for x in xs[:2]:
+            model(x).float().pow(2).mean().backward()
+    model(xs[2]).float().pow(2).mean().backward()
+    sync.finish()
+    assert all(p.grad is None for p in model.parameters())  # micro-batch gradients were folded into main_grad
+    got = torch.cat([p.main_grad.reshape(-1) for p in model.parameters()])
+    # expected: per rank, the fp32 sum of the three bf16 micro-batch gradients; then the mean over ranks in fp32
+    total = None
+    for r in range(world):
+        torch.manual_seed(0)
+        ref = torch.nn.Sequential(torch.nn.Linear(16, 32), torch.nn.Tanh(), torch.nn.Linear(32, 8)).to(torch.bfloat16)
+        gr = torch.Generator().manual_seed(200 + r)
+        acc = None
+        for _ in range(3):
+            ref.zero_grad()
+            ref(torch.randn(4, 16, generator=gr).to(torch.bfloat16)).float().pow(2).mean().backward()
+            v = torch.cat([p.grad.float().reshape(-1) for p in ref.parameters()])
+            acc = v if acc is None else acc + v
+        total = acc if total is None else total + acc
+    out[rank] = float((got - total / world).abs().max())
+    dist.destroy_process_group()
+
+
+def test_grad_sync_fp32_main_grads_gloo_world2():
+    """bf16 parameters: micro-batch gradients accumulate into fp32 main gradients and the reduction runs in fp32
+    (ds_config.json:45), so nothing is rounded to bf16 between the backward that made it and the optimizer."""
+    world = 2
+    port = _free_port()
+    with mp.Manager() as mgr:
+        out = mgr.dict()
+        mp.spawn(_worker_main_grads, args=(world, port, out), nprocs=world, join=True)
+        assert len(out) == world
+        for r in range(world):
+            assert out[r] < 1e-6
+
+
 def test_grad_sync_rejects_cpu_params_for_ftk_backend():
     from kubernetes_cloud_b200 import FtkError
     from kubernetes_cloud_b200.dp import GradSync

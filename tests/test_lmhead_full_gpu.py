@@ -238,3 +238,122 @@ def test_target_beyond_vocabulary_poisons_the_loss(cuda_dev):
     t[17] = V + 3
     loss_sum, n_valid, lse = torch.ops.ftk.lmhead_ce_fwd(H, W, None, t)
     assert torch.isnan(loss_sum).all()
+
+
+# ------------------------------------------------------------------------------------------------ fused fwd + bwd
+def _fused_ctypes(H, W, b, t, dW, dw_code, accumulate, slab_rows, grad_scale=1.0, dbias=None, dw_event=0):
+    from kubernetes_cloud_b200 import _lib
+    L = _lib.lib()
+    M, d = H.shape
+    V = W.shape[0]
+    lse = torch.empty(M, dtype=torch.float32, device="cuda")
+    loss_sum = torch.empty(1, dtype=torch.float32, device="cuda")
+    n_valid = torch.empty(1, dtype=torch.int32, device="cuda")
+    dH = torch.empty_like(H)
+    ws_bytes = L.ftk_lmhead_ce_fused_workspace(M, d, V, slab_rows)
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device="cuda")
+    rc = L.ftk_lmhead_ce_fused(H.data_ptr(), W.data_ptr(), 0 if b is None else b.data_ptr(), t.data_ptr(), M, d, V,
+                               grad_scale, 0, lse.data_ptr(), loss_sum.data_ptr(), n_valid.data_ptr(), dH.data_ptr(),
+                               dW.data_ptr(), dw_code, accumulate, 0 if dbias is None else dbias.data_ptr(), dw_event,
+                               ws.data_ptr(), ws_bytes, slab_rows, torch.cuda.current_stream().cuda_stream)
+    _lib.check(rc, "ftk_lmhead_ce_fused")
+    torch.cuda.synchronize()
+    return float(loss_sum) / max(int(n_valid), 1), int(n_valid), lse, dH
+
+
+@pytest.mark.parametrize("cg", [1, 2])
+@pytest.mark.parametrize("M,d,V,bias,slab", [(128, 64, 256, False, 0), (300, 64, 777, True, 0), (77, 192, 50, False, 0),
+                                             (1000, 256, 5003, True, 256), (1200, 128, 3001, False, 512),
+                                             (2048, 768, 50257, False, 0), (2048, 768, 50257, False, 768)])
+def test_fused_forward_backward_parity(cuda_dev, cta_group, cg, M, d, V, bias, slab):
+    """ftk_lmhead_ce_fused (one call, gradients included) through the C ABI against the fp32 CPU oracle: one slab and
+    several, ragged slabs, bias, both CTA groupings, with and without the dW-done event (dW before dH in the last slab)."""
+    from kubernetes_cloud_b200 import _lib
+    cta_group(cg)
+    g = torch.Generator().manual_seed(M + V)
+    H = torch.randn(M, d, generator=g).to(torch.bfloat16)
+    W = (torch.randn(V, d, generator=g) * 0.05).to(torch.bfloat16)
+    b = (torch.randn(V, generator=g) * 0.5).to(torch.bfloat16) if bias else None
+    t = torch.randint(0, V, (M,), generator=g)
+    t[torch.rand(M, generator=g) < 0.1] = -100
+    want = O.lmhead_ce_reference(H, W, b, t)
+    Hc, Wc, tc = H.cuda(), W.cuda(), t.cuda()
+    bc = None if b is None else b.cuda()
+    dW = torch.full((V, d), float("nan"), device="cuda")
+    db = torch.full((V,), float("nan"), device="cuda") if bias else None
+    ev = torch.cuda.Event()
+    ev.record()  # the handle exists once the event has been recorded
+    loss, n_valid, lse, dH = _fused_ctypes(Hc, Wc, bc, tc, dW, _lib.FTK_F32, 0, slab, grad_scale=0.5, dbias=db,
+                                           dw_event=int(ev.cuda_event) if cg == 2 else 0)
+    if cg == 2:
+        assert ev.query()  # recorded between the last slab's dW and dH GEMMs, long finished by now
+    assert n_valid == want["n_valid"]
+    assert abs(loss - float(want["loss"])) <= LOSS_RTOL * abs(float(want["loss"]))
+    assert float((lse.cpu() - want["lse"]).abs().max()) < 2e-3
+    assert O.rel_err(dH.float(), 0.5 * want["dH"]) < GRAD_RTOL
+    assert O.rel_err(dW, 0.5 * want["dW"]) < GRAD_RTOL
+    if bias:
+        assert O.rel_err(db, 0.5 * want["dbias"]) < GRAD_RTOL
+    assert float(dH[tc == -100].abs().max()) == 0.0
+    # bf16 dW accumulated on top of existing content
+    before = (torch.randn(V, d, generator=g) * float(want["dW"].std())).to(torch.bfloat16)
+    dW16 = before.cuda().clone()
+    _fused_ctypes(Hc, Wc, bc, tc, dW16, _lib.FTK_BF16, 1, slab)
+    assert O.rel_err(dW16.float(), before.float() + want["dW"]) < GRAD_RTOL
+
+
+def test_fused_mode_at_the_headline_shape(cuda_dev):
+    """The default training path at (16384, 2048, 50257): two 8192-row slabs.  lse / loss / sampled dW rows / sampled
+    dH rows against dense fp32 torch recomputations; every quantity against the recompute path of the same library."""
+    from kubernetes_cloud_b200 import _lib, ops  # noqa: F401
+    M, d, V = 16384, 2048, 50257
+    H, W, _, t = gpu_inputs(M, d, V, seed=11, bias=False)
+    assert 0 < _lib.lib().ftk_lmhead_ce_fused_slab_rows(M, d, V, 0) < M
+    loss_sum, n_valid, lse, dH, dW, _ = torch.ops.ftk.lmhead_ce_fused(H, W, None, t, 1.0, False, 0)
+    lse_ref = dense_lse(H, W, None)
+    assert int(n_valid) == int((t >= 0).sum())
+    assert float((lse - lse_ref).abs().max()) < 2e-3
+    vs = sampled_vocab_rows(V, t)
+    dW_ref, _ = dense_dw_rows(H, W, None, t, lse_ref, vs)
+    assert O.rel_err(dW[vs].float(), dW_ref) < GRAD_RTOL
+    ls2, nv2, lse2 = torch.ops.ftk.lmhead_ce_fwd(H, W, None, t)
+    dH2, dW2, _ = torch.ops.ftk.lmhead_ce_bwd(H, W, None, t, lse2, None, nv2, 1.0, False)
+    assert abs(float(loss_sum) - float(ls2)) <= 1e-5 * abs(float(ls2))
+    assert float((lse - lse2).abs().max()) < 1e-4
+    assert O.rel_err(dH.float(), dH2.float()) < 5e-3 and O.rel_err(dW.float(), dW2.float()) < 5e-3
+    assert float(dH[t < 0].abs().max()) == 0.0
+
+
+def test_fused_autograd_loss_scale_and_upstream_gradient(cuda_dev):
+    """fused_lmhead_ce in its default mode: loss_scale is folded into the gradients made during the forward; an
+    upstream gradient other than 1 is applied by the rescaling pass; a weight gradient accumulated in place with an
+    upstream gradient other than 1 poisons dH instead of passing silently."""
+    from kubernetes_cloud_b200 import ops
+    M, d, V = 700, 128, 3001
+    g = torch.Generator().manual_seed(5)
+    H = torch.randn(M, d, generator=g).to(torch.bfloat16)
+    W = (torch.randn(V, d, generator=g) * 0.05).to(torch.bfloat16)
+    b = (torch.randn(V, generator=g) * 0.5).to(torch.bfloat16)
+    t = torch.randint(0, V, (M,), generator=g)
+    t[::7] = -100
+    want = O.lmhead_ce_reference(H, W, b, t)
+    ops.set_fused_slab_rows(256)
+    try:
+        Hc, Wc, bc = (x.cuda().requires_grad_(True) for x in (H, W, b))
+        loss = ops.fused_lmhead_ce(Hc, Wc, bc, t.cuda(), loss_scale=0.25)
+        assert abs(float(loss.detach()) - 0.25 * float(want["loss"])) <= LOSS_RTOL * 0.25 * float(want["loss"])
+        (loss * 2.0).backward()  # upstream gradient 2 on top of loss_scale 0.25
+        assert O.rel_err(Hc.grad.float(), 0.5 * want["dH"]) < GRAD_RTOL
+        assert O.rel_err(Wc.grad.float(), 0.5 * want["dW"]) < GRAD_RTOL
+        assert O.rel_err(bc.grad.float(), 0.5 * want["dbias"]) < 2e-2  # bf16 bias gradient
+        with pytest.raises(Exception):
+            loss.backward()
+        # in-place accumulation + upstream gradient 1: exact; + upstream gradient != 1: poisoned
+        Hc2 = H.cuda().requires_grad_(True)
+        ops.fused_lmhead_ce(Hc2, Wc, None, t.cuda()).backward()
+        assert torch.isfinite(Hc2.grad).all()
+        Hc3 = H.cuda().requires_grad_(True)
+        (ops.fused_lmhead_ce(Hc3, Wc, None, t.cuda()) * 3.0).backward()
+        assert torch.isnan(Hc3.grad).all()
+    finally:
+        ops.set_fused_slab_rows(0)

@@ -13,13 +13,14 @@ def _model(dtype):
     return m.cuda().to(dtype)
 
 
-@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
-def test_fused_adamw_matches_torch_adamw(cuda_dev, dtype):
+@pytest.mark.parametrize("dtype,main_grads", [(torch.float32, False), (torch.bfloat16, False), (torch.bfloat16, True)])
+def test_fused_adamw_matches_torch_adamw(cuda_dev, dtype, main_grads):
     from kubernetes_cloud_b200.dp import GradSync
     from kubernetes_cloud_b200.optim import FusedAdamW, WarmupLR
     model = _model(dtype)
     params0 = [p.detach().clone() for p in model.parameters()]
-    sync = GradSync(model.parameters(), 0, 1, bucket_bytes=8 << 10, backend="ftk")
+    sync = GradSync(model.parameters(), 0, 1, bucket_bytes=8 << 10, backend="ftk", main_grads=main_grads)
+    assert sync.buckets[0].flat.dtype == (torch.float32 if main_grads else dtype)
     sched = WarmupLR(max_lr=1e-2, warmup_steps=4)
     opt = FusedAdamW(sync, lr=1e-2, weight_decay=0.01, max_grad_norm=0.5, schedule=sched)
     g = torch.Generator().manual_seed(5)
@@ -28,7 +29,7 @@ def test_fused_adamw_matches_torch_adamw(cuda_dev, dtype):
         sync.zero_grad()
         grads = [(torch.randn(p.shape, generator=g) * (3.0 if step % 2 else 0.05)).to(dtype) for p in params0]
         for p, gr in zip(model.parameters(), grads):
-            p.grad.copy_(gr.cuda())  # gradients land in the bucket views
+            (p.main_grad if main_grads else p.grad).copy_(gr.cuda())  # gradients land in the bucket views
         lrs.append(opt.current_lr())
         opt.step()
         norms.append(float(opt.grad_norm()))
