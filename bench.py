@@ -350,8 +350,14 @@ def main_gpu(args) -> None:
     barrier()
     sampler.mark_end()
     clocks = sampler.stop() if rank == 0 else None
-    timeline = _lib.timeline_read()
+    trace = _lib.timeline_read(with_start=True)
+    timeline = [(n_, ms_) for n_, ms_, _ in trace]
     _lib.timeline_enable(False)
+    if os.environ.get("FTK_BENCH_TRACE") and rank == 0:  # start / duration of every launch of the last two steps
+        per = len(trace) // max(args.steps, 1)
+        for n_, ms_, st_ in trace[-2 * per:]:
+            print(f"trace {st_:10.3f} ms  +{ms_:7.3f}  {n_}", file=sys.stderr)
+        print(f"trace: GradSync launched {sync.launched} all-reduces in {args.warmup + args.steps} steps", file=sys.stderr)
     # ours: gather + fused call + rescale checks (counted in ops) + grad-norm, clip, AdamW per step
     launches = ops.launch_count() - l0 + 3 * args.steps
     ms_total = max_over_ranks(t_begin.elapsed_time(t_end))

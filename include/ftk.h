@@ -73,7 +73,10 @@ int ftk_set_option(int32_t key, int32_t value);
  *                           two CUDA events on its own stream (host cost: two cudaEventRecord per launch)
  *   ftk_timeline_enable(0)  stops recording and clears
  *   ftk_timeline_read       waits for the recorded events, writes (tag, milliseconds) pairs in launch order and
- *                           returns how many (<= max_n); negative on error. Do not call it during stream capture.
+ *                           returns how many (<= max_n); negative on error. start_ms (optional) receives each
+ *                           launch's start relative to the first recorded launch, across streams, so gaps and
+ *                           overlap (compute stream vs communication stream) can be read off. Do not call it during
+ *                           stream capture.
  * Tags name the kernels of this library.
  */
 #define FTK_TL_GATHER 1
@@ -87,8 +90,9 @@ int ftk_set_option(int32_t key, int32_t value);
 #define FTK_TL_DBIAS 9
 #define FTK_TL_ADAMW 10
 #define FTK_TL_SQNORM 11
+#define FTK_TL_ALLREDUCE 12 /* the NCCL collective, on the communication stream */
 int ftk_timeline_enable(int32_t on);
-int ftk_timeline_read(int32_t* tags, float* ms, int32_t max_n);
+int ftk_timeline_read(int32_t* tags, float* ms, float* start_ms, int32_t max_n);
 
 /*
  * Window gather + label/mask construction, one launch per micro-batch.

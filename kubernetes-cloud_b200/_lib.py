@@ -46,7 +46,7 @@ SIGNATURES = {
                                     c_void_p, c_size_t, c_void_p]),
     "ftk_set_option": (c_int32, [c_int32, c_int32]),
     "ftk_timeline_enable": (c_int32, [c_int32]),
-    "ftk_timeline_read": (c_int32, [c_void_p, c_void_p, c_int32]),
+    "ftk_timeline_read": (c_int32, [c_void_p, c_void_p, c_void_p, c_int32]),
     "ftk_set_sm_reserve": (c_int32, [c_int32]),
     "ftk_dp_unique_id": (c_int32, [c_void_p]),
     "ftk_dp_init": (c_int32, [c_void_p, c_int32, c_int32, POINTER(c_void_p)]),
@@ -114,18 +114,22 @@ def set_option(name: str, value: int) -> None:
 
 
 TIMELINE_TAGS = {1: "gather", 2: "fwd", 3: "fwd_keep", 4: "finalize", 5: "dz", 6: "convert", 7: "dH", 8: "dW",
-                 9: "dbias", 10: "adamw", 11: "sqnorm"}  # FTK_TL_* in include/ftk.h
+                 9: "dbias", 10: "adamw", 11: "sqnorm", 12: "allreduce"}  # FTK_TL_* in include/ftk.h
 
 
 def timeline_enable(on: bool) -> None:
     check(lib().ftk_timeline_enable(int(on)), "ftk_timeline_enable")
 
 
-def timeline_read(max_n: int = 1 << 16):
-    """[(kernel name, milliseconds)] for every tagged launch since ``timeline_enable(True)``; waits for them."""
+def timeline_read(max_n: int = 1 << 16, with_start: bool = False):
+    """[(kernel name, milliseconds)] for every tagged launch since ``timeline_enable(True)``; waits for them.
+    ``with_start``: triples (name, milliseconds, start in ms after the first launch) -- a small trace across streams."""
     tags = (c_int32 * max_n)()
     ms = (c_float * max_n)()
-    n = lib().ftk_timeline_read(tags, ms, max_n)
+    st = (c_float * max_n)()
+    n = lib().ftk_timeline_read(tags, ms, st if with_start else None, max_n)
     if n < 0:
         check(n, "ftk_timeline_read")
+    if with_start:
+        return [(TIMELINE_TAGS.get(tags[i], str(tags[i])), ms[i], st[i]) for i in range(n)]
     return [(TIMELINE_TAGS.get(tags[i], str(tags[i])), ms[i]) for i in range(n)]

@@ -103,7 +103,7 @@ extern "C" int ftk_timeline_enable(int32_t on) {
   return FTK_OK;
 }
 
-extern "C" int ftk_timeline_read(int32_t* tags, float* ms, int32_t max_n) {
+extern "C" int ftk_timeline_read(int32_t* tags, float* ms, float* start_ms, int32_t max_n) {
   FTK_REQUIRE(tags && ms && max_n >= 0, "ftk_timeline_read: bad arguments");
   std::lock_guard<std::mutex> lk(ftk::g_tl_mu);
   int n = 0;
@@ -114,6 +114,11 @@ extern "C" int ftk_timeline_read(int32_t* tags, float* ms, int32_t max_n) {
     FTK_CUDA_CHECK(cudaEventElapsedTime(&t, e.a, e.b));
     tags[n] = e.tag;
     ms[n] = t;
+    if (start_ms != nullptr) {
+      float s0 = 0.f;
+      FTK_CUDA_CHECK(cudaEventElapsedTime(&s0, ftk::g_tl.front().a, e.a));  // works across streams
+      start_ms[n] = s0;
+    }
     ++n;
   }
   return n;

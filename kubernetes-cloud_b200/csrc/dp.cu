@@ -210,6 +210,7 @@ extern "C" int ftk_dp_allreduce_after(ftk_dp_t* dp, void* buf, size_t count, int
 }
 
 static int allreduce_on_comm_stream(ftk_dp_t* dp, void* buf, size_t count, int32_t dtype, float prescale) {
+  ftk::TimelineScope tl_(FTK_TL_ALLREDUCE, dp->comm_stream);
   // The scale is folded into the collective (ncclAvg for 1/world, a pre-multiplied sum otherwise): a separate
   // scaling kernel on the comm stream would have to squeeze through whatever SMs a concurrent persistent GEMM left
   // free and delays the all-reduce by about a millisecond (profiles/r01_overlap_probe.txt).

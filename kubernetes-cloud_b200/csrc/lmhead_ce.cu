@@ -1046,7 +1046,7 @@ int run_fwd(const void* H, const void* W, const void* bias, const int64_t* targe
 template <int kCG>
 int run_fwd_keep(const void* H, const void* W, const void* bias, const int64_t* targets, int64_t M, int d, int V,
                  float* lse, float* loss_sum, int32_t* n_valid, __nv_bfloat16* probs, float* cref,
-                 const FwdWorkspace& ws, int sm_count, cudaStream_t st, int add_to_loss = 0) {
+                 const FwdWorkspace& ws, int sm_count, cudaStream_t st, int add_to_loss = 0, int reserve = -1) {
   constexpr int BN = 256;
   constexpr int kStages = (kCG == 1) ? 4 : 6;
   const int64_t ld = round_up(V, 64);
@@ -1057,8 +1057,8 @@ int run_fwd_keep(const void* H, const void* W, const void* bias, const int64_t* 
   const int n_mblk = ceil_div(M, BM * kCG);
   sc.n_ntile = ceil_div(V, BN);
   int n_chunks;
-  plan_chunks(n_mblk, sc.n_ntile, (sm_count - sm_reserve() > kCG ? sm_count - sm_reserve() : kCG) / kCG, &n_chunks,
-              &sc.tiles_per_chunk);
+  const int usable = sm_count - (reserve >= 0 ? reserve : sm_reserve());
+  plan_chunks(n_mblk, sc.n_ntile, (usable > kCG ? usable : kCG) / kCG, &n_chunks, &sc.tiles_per_chunk);
   sc.n_units = n_mblk * n_chunks;
   sc.n_mblk = n_mblk;
   sc.n_chunks = n_chunks;
@@ -1080,7 +1080,7 @@ int run_fwd_keep(const void* H, const void* W, const void* bias, const int64_t* 
   FTK_CUDA_CHECK(cudaMemsetAsync(ws.ticket, 0, sizeof(unsigned int), st));
 {
     ftk::TimelineScope tl_(FTK_TL_FWD_KEEP, st);
-    if (int rc = launch_umma<kCG, BN, kStages, false, false, FwdKeepEpi>(tmA, tmB, sc, ep, sm_count, st)) return rc;
+    if (int rc = launch_umma<kCG, BN, kStages, false, false, FwdKeepEpi>(tmA, tmB, sc, ep, sm_count, st, reserve)) return rc;
   }
   fwd_finalize_kernel<<<ceil_div(M, 256), 256, 0, st>>>(ws.pmax, ws.psum, ws.ztgt, targets, static_cast<int>(M),
                                                         static_cast<int>(ws.Mpad), V, n_chunks, lse, ws.blk_loss,
@@ -1555,9 +1555,9 @@ extern "C" int ftk_lmhead_ce_fused(const void* H, const void* W, const void* bia
     const FwdWorkspace ws = carve_fwd(fw.fwd, rows);
     // (1) logits tile by tile: softmax statistics + bf16 numerators of this slab; (2) lse and the slab's loss
     int rc = pair ? run_fwd_keep<2>(Hs, W, bias, targets + r0, rows, d, V, lse + r0, loss_sum, nullptr, fw.probs,
-                                    fw.cref, ws, di.sm_count, st, 1)
+                                    fw.cref, ws, di.sm_count, st, 1, 0)
                   : run_fwd_keep<1>(Hs, W, bias, targets + r0, rows, d, V, lse + r0, loss_sum, nullptr, fw.probs,
-                                    fw.cref, ws, di.sm_count, st, 1);
+                                    fw.cref, ws, di.sm_count, st, 1, 0);
     if (rc) return rc;
     // (3) numerators -> dZ in place
     {

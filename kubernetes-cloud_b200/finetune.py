@@ -9,8 +9,10 @@ FT.py:987-998; per-step samples/s as ``PerformanceCallback`` computes it, FT.py:
 pieces: ``TokenizedDataset`` + ``DeviceBatcher`` for the dataset/collator/H2D path, ``compute_loss`` for lm_head + loss,
 ``GradSync`` for DeepSpeed's gradient reduction, ``FusedAdamW`` + ``WarmupLR`` for its optimizer.  The transformer
 trunk is the HF model (third-party, out of this tier's scope).  Flags of the reference that configure things outside
-the hot path (wandb, Tensorizer, prompt sampling, checkpoint discovery) are accepted and ignored with a log line, so
-the workflow's flag string (finetune-workflow.yaml:267-300) parses unchanged.
+the hot path (wandb, Tensorizer, prompt sampling, checkpoint discovery) are parsed with the reference's own types,
+defaults and validation and then only logged, so the workflow's flag string (finetune-workflow.yaml:267-300) parses
+verbatim (tests/test_host_logic.py feeds it through ``build_parser``).  ``--fp16=true`` is rejected with exit code 1:
+the kernels compute in bf16 and serving fp16 requests in bf16 silently would misreport the run.
 
 There is no network in the build environment: ``--model`` is an architecture name (random-init from the literal HF
 config, as BASELINE.json's configs ask), or a local directory / config.json.
@@ -39,10 +41,49 @@ ARCHS = {
     "gpt-j-6b": ("gptj", dict()),          # GPTJConfig() defaults: 4096 / 28 / 16, V 50400, untied, lm_head bias
 }
 
-IGNORED_FLAGS = ["--cache", "--output-path", "--logs", "--save-steps", "--project-id", "--prompt-file",
-                 "--prompt-every", "--prompt-tokens", "--prompt-samples", "--top-k", "--top-p", "--temperature",
-                 "--repetition-penalty", "--tensorizer-uri", "--zero-stage", "--train-ratio", "--force-fp32-attn"]
-IGNORED_BOOLS = ["--no-resume", "--fp16"]
+class FuzzyBool(argparse.Action):
+    """Boolean flag with the reference's grammar (utils.py:229-292): bare ``--flag`` or ``--flag=<text>``, where the
+    texts 0 / no / f / false (any case) mean "as if the flag were absent" and anything else "as if it were present".
+    Present = ``not default``, so a flag declared with ``default=True`` and another ``dest`` (``--no-shuffle`` ->
+    ``shuffle``) is inverted: ``--no-shuffle`` and ``--no-shuffle=true`` give shuffle False, ``--no-shuffle=false``
+    gives True."""
+
+    def __init__(self, option_strings, dest, default=False, help=None, **_):
+        if not isinstance(default, bool):
+            raise ValueError("FuzzyBool needs a boolean default")
+        absent, present = default, not default
+        super().__init__(option_strings, dest, nargs="?", const=present, default=absent, metavar="BOOL", help=help,
+                         type=lambda text: absent if text.strip().lower() in ("0", "no", "f", "false") else present)
+
+    def __call__(self, parser, namespace, values, option_string=None):
+        setattr(namespace, self.dest, values)
+
+
+def _number(kind, low=None, low_open=False, high=None, also=None):
+    """argparse ``type=`` that parses ``kind`` and enforces a range, with one optional extra allowed value
+    (the reference's validators, utils.py:297-356: positive, non-negative, at most 1, -1 as a special value)."""
+    def parse(text: str):
+        v = kind(text)
+        if also is not None and v == also:
+            return v
+        if low is not None and (v <= low if low_open else v < low):
+            raise argparse.ArgumentTypeError(f"must be {'greater than' if low_open else 'at least'} {low}, not {v}")
+        if high is not None and v > high:
+            raise argparse.ArgumentTypeError(f"must be at most {high}, not {v}")
+        return v
+    return parse
+
+
+def _file(optional: bool):
+    def parse(text: str) -> str:
+        if not text:
+            if optional:
+                return ""
+            raise argparse.ArgumentTypeError("must be specified")
+        if not os.path.isfile(text):
+            raise argparse.ArgumentTypeError(f"file not found: {text}")
+        return text
+    return parse
 
 
 class DashParser(argparse.ArgumentParser):
@@ -56,32 +97,80 @@ class DashParser(argparse.ArgumentParser):
         return super().add_argument(*names, *extra, **kw)
 
 
+# flags of the reference that configure things outside the hot path: parsed with the reference's types and defaults,
+# then only logged
+OUTSIDE_HOT_PATH = ["trust_remote_code", "tensorizer_uri", "train_ratio", "zero_stage", "output_path", "resume", "cache",
+                    "save_steps", "project_id", "logs", "ds_config", "fp16_full_eval", "prompt_file", "prompt_every",
+                    "prompt_tokens", "prompt_samples", "top_k", "top_p", "temperature", "repetition_penalty"]
+
+
 def build_parser() -> DashParser:
+    """Every flag of the reference's parser (FT.py:61-274) with its type, default and validation, so the flag string the
+    workflow builds (finetune-workflow.yaml:267-300) parses verbatim; plus a few of this CLI's own at the end."""
+    from decimal import Decimal
     p = DashParser(description="B200 finetuner (reference-compatible flags)")
     p.add_argument("--run-name", type=str, required=True)
     p.add_argument("--model", type=str, required=True, help="architecture name, local model directory or config.json")
-    p.add_argument("--dataset", type=str, required=True, help="pre-tokenized uint16 file (FT.py:81-86)")
-    p.add_argument("--lr", type=float, default=5e-5)
-    p.add_argument("--epochs", type=int, default=1)
-    p.add_argument("--bs", type=int, default=1, help="micro-batch per GPU; the reference's -1 (estimate) is not kept")
-    p.add_argument("--gradients", type=int, default=5, help="gradient accumulation steps (FT.py:135-140)")
-    p.add_argument("--seed", type=int, default=42)
-    p.add_argument("--context-size", type=int, default=2048)
-    p.add_argument("--warmup-ratio", type=float, default=0.1)
+    p.add_argument("--trust-remote-code", action=FuzzyBool, default=False)
+    p.add_argument("--dataset", type=_file(optional=False), required=True, help="pre-tokenized uint16 file")
+    p.add_argument("--tensorizer-uri", type=str, default="")
+    p.add_argument("--lr", type=_number(float, low=0), default=5e-5)
+    p.add_argument("--epochs", type=_number(int, low=0, low_open=True), default=1)
+    p.add_argument("--train-ratio", type=_number(Decimal, low=0, high=1), default=Decimal("0.9"))
+    p.add_argument("--warmup-ratio", type=_number(Decimal, low=0, high=1), default=Decimal("0.1"))
     p.add_argument("--eot", type=str, default="")
     p.add_argument("--pad", type=str, default="")
+    p.add_argument("--bs", type=_number(int, low=0, low_open=True, also=-1), default=-1,
+                   help="micro-batch per GPU (-1 = size it from free device memory)")
+    p.add_argument("--bs-divisor", type=_number(Decimal, low=0, low_open=True), default=Decimal(1))
+    p.add_argument("--gradients", type=_number(int, low=0, low_open=True), default=5,
+                   help="gradient accumulation steps (FT.py:135-140)")
+    p.add_argument("--zero-stage", type=int, default=3, choices=range(0, 4))
+    p.add_argument("--seed", type=_number(int, low=0, high=(1 << 32) - 1), default=42)
+    p.add_argument("--output-path", type=str, default="./")
+    p.add_argument("--no-resume", action=FuzzyBool, dest="resume", default=True)
+    p.add_argument("--cache", type=str, default="/tmp")
+    p.add_argument("--save-steps", type=_number(int, low=0), default=500)
+    p.add_argument("--context-size", type=_number(int, low=0, low_open=True), default=2048)
+    p.add_argument("--project-id", type=str, default="huggingface")
+    p.add_argument("--logs", type=str, default="./logs")
+    p.add_argument("--ds-config", type=_file(optional=True), default="")
+    p.add_argument("--fp16", action=FuzzyBool, default=False)
+    p.add_argument("--fp16-full-eval", action=FuzzyBool, default=False)
+    p.add_argument("--no-shuffle", action=FuzzyBool, dest="shuffle", default=True)
+    p.add_argument("--prompt-file", type=_file(optional=True))
+    p.add_argument("--prompt-every", type=_number(int, low=0, also=-1), default=0)
+    p.add_argument("--prompt-tokens", type=_number(int, low=0), default=200)
+    p.add_argument("--prompt-samples", type=_number(int, low=0), default=5)
+    p.add_argument("--top-k", type=_number(int, low=0), default=50)
+    p.add_argument("--top-p", type=_number(float, low=0, high=1), default=0.95)
+    p.add_argument("--temperature", type=_number(float, low=0, low_open=True), default=1.0)
+    p.add_argument("--repetition-penalty", type=_number(float, low=0, low_open=True), default=1.1)
+    p.add_argument("--local-rank", type=_number(int, low=0, also=-1), default=-1)
+    p.add_argument("--log-level", type=str.upper, default="INFO",
+                   choices=("DEBUG", "INFO", "WARNING", "ERROR", "CRITICAL"))
+    # this CLI's own (no network here, so ids instead of a tokenizer download; bounded runs; a metrics file)
     p.add_argument("--pad-token-id", type=int, default=50256, help="used instead of a tokenizer download")
     p.add_argument("--eos-token-id", type=int, default=50256)
-    p.add_argument("--no-shuffle", action="store_false", dest="shuffle")
-    p.add_argument("--local-rank", type=int, default=-1)
     p.add_argument("--max-steps", type=int, default=-1, help="stop after this many optimizer steps")
     p.add_argument("--max-grad-norm", type=float, default=1.0)
     p.add_argument("--report-json", type=str, default="", help="write per-step metrics here")
-    for f in IGNORED_FLAGS:
-        p.add_argument(f, type=str, default=None)
-    for f in IGNORED_BOOLS:
-        p.add_argument(f, nargs="?", const="true", default=None)
     return p
+
+
+def estimate_batch_size(device, divisor, per_context_bytes: int) -> int:
+    """--bs=-1.  The reference sizes the micro-batch as ceil(free device memory / (memory torch holds after loading the
+    model x divisor)) (FT.py:447-466).  Same quantities and rounding here; the result is additionally capped by what
+    the step itself is known to need per context (gradient-checkpointed activations + the hot path's per-token
+    buffers), so the first step cannot run out of memory on a card with 180 GB."""
+    import math
+    torch.cuda.synchronize(device)
+    torch.cuda.empty_cache()
+    free, _total = torch.cuda.mem_get_info(device)
+    used = max(torch.cuda.memory_allocated(device), 1)
+    by_reference_rule = math.ceil(free / (used * float(divisor)))
+    by_step_need = max(1, int(free * 0.6 // max(per_context_bytes, 1)))
+    return max(1, min(by_reference_rule, by_step_need))
 
 
 def load_model(spec: str):
@@ -100,12 +189,21 @@ def load_model(spec: str):
 
 
 def main(argv: Optional[List[str]] = None) -> dict:
-    args = build_parser().parse_args(argv)
-    logging.basicConfig(level=logging.INFO, format="%(asctime)s %(name)s %(levelname)s %(message)s")
-    for f in IGNORED_FLAGS + IGNORED_BOOLS:
-        v = getattr(args, f[2:].replace("-", "_"))
-        if v is not None:
-            logger.info("flag %s=%s is outside the hot path and is ignored here", f, v)
+    parser = build_parser()
+    args = parser.parse_args(argv)
+    logging.basicConfig(level=getattr(logging, args.log_level), format="%(asctime)s %(name)s %(levelname)s %(message)s")
+    defaults = vars(parser.parse_args(["--run-name", "x", "--model", "x", "--dataset", args.dataset]))
+    for name in OUTSIDE_HOT_PATH:
+        if getattr(args, name) != defaults[name]:
+            logger.info("flag --%s=%s configures something outside the hot path and has no effect here",
+                        name.replace("_", "-"), getattr(args, name))
+    if args.fp16:
+        # FT.py:195-200, :775-779, :791: fp16 weights with DeepSpeed's dynamic loss scaling.  The kernels here take
+        # bf16 operands (same exponent range as fp32, so no loss scaling); serving the flag in bf16 silently would
+        # change the run's numerics behind the user's back.
+        logger.error("--fp16 is not supported by the B200 hot path (bf16 operands, fp32 accumulation); "
+                     "drop the flag or pass --fp16=false")
+        sys.exit(1)
 
     import torch.distributed as dist
     from . import DeviceBatcher, FusedAdamW, GradSync, TokenizedDataset, WarmupLR, validate_token_file
@@ -142,44 +240,62 @@ def main(argv: Optional[List[str]] = None) -> dict:
     if rep.max_token >= model.config.vocab_size:
         raise SystemExit(f"token id {rep.max_token} does not fit the model's vocabulary {model.config.vocab_size}")
 
-    batcher = DeviceBatcher(ds, args.bs, seed=args.seed, shuffle=args.shuffle, rank=rank, world=world, shift_labels=True)
+    bs = args.bs
+    if bs == -1:  # FT.py:892-895
+        cfg = model.config
+        d_model = getattr(cfg, "hidden_size", getattr(cfg, "n_embd", 2048))
+        n_layer = getattr(cfg, "num_layers", getattr(cfg, "n_layer", getattr(cfg, "num_hidden_layers", 24)))
+        # per context: one checkpointed residual per layer + ~12 live activations of the layer being recomputed
+        # (bf16), the hot path's hidden / dH rows and its share of the numerators slab
+        per_ctx = args.context_size * (d_model * 2 * (n_layer + 12 + 2) + 2 * 2 * ((cfg.vocab_size + 63) // 64 * 64))
+        bs = estimate_batch_size(dev, args.bs_divisor, per_ctx)
+    if main_proc:
+        logger.info("BS: %d", bs)
+        logger.info("GAS: %d", args.gradients)
+    # the split order is drawn once (FT.py:761); every epoch the Trainer's sampler re-shuffles it (seed + epoch)
+    batcher = DeviceBatcher(ds, bs, seed=args.seed, shuffle=args.shuffle, rank=rank, world=world, shift_labels=True,
+                            trainer_sampler=args.shuffle)
     micro_per_epoch = batcher.batches_per_epoch()
-    steps_per_epoch = max(1, micro_per_epoch // args.gradients)
+    # HF Trainer steps once every GAS micro-batches and once more on a shorter tail at the end of the epoch
+    steps_per_epoch = (micro_per_epoch + args.gradients - 1) // args.gradients
     total_steps = steps_per_epoch * args.epochs
     if args.max_steps > 0:
         total_steps = min(total_steps, args.max_steps)
     sync = GradSync(model.parameters(), rank, world)
     opt = FusedAdamW(sync, lr=args.lr, weight_decay=0.01, max_grad_norm=args.max_grad_norm,
-                     schedule=WarmupLR(args.lr, max(2, int(args.warmup_ratio * total_steps))))
+                     schedule=WarmupLR(args.lr, max(2, int(float(args.warmup_ratio) * total_steps))))
 
     history = []
     step = 0
     for epoch in range(args.epochs):
+        batcher.set_epoch(epoch)
         it = batcher.epoch()
-        for _ in range(steps_per_epoch):
+        for s_in_epoch in range(steps_per_epoch):
             if step >= total_steps:
                 break
             t0 = time.time()
             sync.zero_grad()
             losses = []
-            for g in range(args.gradients):
+            # the last step of an epoch may have fewer micro-batches than GAS (micro_per_epoch % GAS of them)
+            n_micro = min(args.gradients, micro_per_epoch - s_in_epoch * args.gradients)
+            for g in range(n_micro):
                 batch = next(it)
                 n_valid = batch.pop("n_valid")  # noqa: F841  (per-row counts; the fused loss recounts)
-                last = g == args.gradients - 1
+                last = g == n_micro - 1
                 ctx = sync.no_sync() if not last else _null()
                 with ctx:
                     # HF Trainer scales the loss by 1/GAS before backward; here the factor goes into the fused loss,
                     # whose gradients are made during the forward call
-                    loss = compute_loss(model, batch, labels_are_shifted=True, loss_scale=1.0 / args.gradients)
+                    loss = compute_loss(model, batch, labels_are_shifted=True, loss_scale=1.0 / n_micro)
                     loss.backward()
-                losses.append(loss.detach() * args.gradients)
+                losses.append(loss.detach() * n_micro)
             sync.finish()
             lr_used = opt.current_lr()
             opt.step()
             torch.cuda.synchronize(dev)
             dt = time.time() - t0
             mean_loss = float(torch.stack(losses).mean())
-            rank_sps = args.bs * args.gradients / dt  # FT.py:516-522
+            rank_sps = bs * n_micro / dt  # FT.py:516-522
             rec = {"step": step, "loss": mean_loss, "lr": lr_used, "grad_norm": float(opt.grad_norm()),
                    "rank_samples_per_second": rank_sps, "world_samples_per_second": world * rank_sps,
                    "tokens_per_second": world * rank_sps * args.context_size, "step_time": dt}

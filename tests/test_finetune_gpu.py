@@ -27,10 +27,10 @@ def test_finetune_cli_runs_and_learns(cuda_dev, tmp_path):
     rep = str(tmp_path / "rep.json")
     argv = ["--run_name", "t", "--model", str(cfg_dir), "--dataset", path, "--context_size", str(T), "--bs", "2",
             "--gradients", "2", "--lr", "3e-3", "--epochs", "2", "--max-steps", "12", "--warmup-ratio", "0.1",
-            "--pad-token-id", str(V - 1), "--eos-token-id", str(V - 1), "--zero_stage", "3", "--fp16", "--no_resume",
-            "--report-json", rep, "--seed", "42"]
+            "--pad-token-id", str(V - 1), "--eos-token-id", str(V - 1), "--zero_stage", "3", "--fp16=false",
+            "--no_resume", "--report-json", rep, "--seed", "42"]
     ns = build_parser().parse_args(argv)
-    assert ns.context_size == T and ns.shuffle is True and ns.zero_stage == "3"
+    assert ns.context_size == T and ns.shuffle is True and ns.zero_stage == 3 and ns.resume is False
     out = main(argv)
     hist = out["history"]
     assert out["steps"] == 12 and len(hist) == 12
@@ -40,3 +40,26 @@ def test_finetune_cli_runs_and_learns(cuda_dev, tmp_path):
     assert hist[0]["lr"] < hist[-1]["lr"] <= 3e-3 + 1e-12    # WarmupLR
     assert hist[0]["tokens_per_second"] > 0
     assert json.load(open(rep))["steps"] == 12
+
+
+def test_finetune_cli_short_epoch_tail_and_auto_batch_size(cuda_dev, tmp_path):
+    """Fewer micro-batches per epoch than --gradients, and a remainder: 7 contexts at --bs 2 are 4 micro-batches;
+    with --gradients 3 an epoch is one step of 3 and one of 1 (HF Trainer steps on the short tail), each averaging
+    over the micro-batches it really had.  Two epochs walk different orders.  --bs=-1 sizes the batch itself."""
+    from transformers import GPTNeoConfig
+    from kubernetes_cloud_b200 import write_token_file
+    from kubernetes_cloud_b200.finetune import main
+    T, V = 64, 300
+    cfg_dir = tmp_path / "tiny"
+    cfg_dir.mkdir()
+    GPTNeoConfig(vocab_size=V, hidden_size=64, num_layers=1, num_heads=2, max_position_embeddings=T,
+                 attention_types=[[["global"], 1]], window_size=16).save_pretrained(str(cfg_dir))
+    path = str(tmp_path / "d.tokens")
+    write_token_file(path, np.random.default_rng(1).integers(0, V - 1, size=7 * T - 5), T, pad_id=V - 1)
+    base = ["--run-name", "t", "--model", str(cfg_dir), "--dataset", path, "--context-size", str(T),
+            "--pad-token-id", str(V - 1), "--eos-token-id", str(V - 1)]
+    out = main(base + ["--bs", "2", "--gradients", "3", "--epochs", "2"])
+    assert out["steps"] == 4 and all(math.isfinite(h["loss"]) for h in out["history"])
+    assert out["history"][0]["loss"] != out["history"][2]["loss"]  # second epoch: reshuffled order, updated weights
+    out = main(base + ["--gradients", "8", "--max-steps", "1"])     # --bs defaults to -1; 7 contexts < bs * gradients
+    assert out["steps"] == 1 and math.isfinite(out["history"][0]["loss"])

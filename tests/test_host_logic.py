@@ -207,3 +207,111 @@ def test_sampler_epoch_order_matches_distributed_sampler_over_the_split():
                 want = [train[i] for i in smp]           # dataset items = context indices
                 got = sampler_epoch_order(split, seed, epoch, rank, world)
                 assert [int(v) for v in got] == want
+
+
+# ------------------------------------------------------------------------------------------------ CLI boundary
+# The flag string the workflow hands to finetuner.py (finetune-workflow.yaml:267-300), templates as written there,
+# and the workflow's own default parameter values (finetune-workflow.yaml:8-199).
+WORKFLOW_FLAGS = """
+--run-name={{workflow.parameters.run_name}}
+--model=/{{workflow.parameters.pvc}}/models/{{workflow.parameters.model}}
+--trust-remote-code={{workflow.parameters.trust_remote_code}}
+--dataset {{DATASET}}
+--tensorizer-uri='{{workflow.parameters.tensorizer_uri}}'
+--lr={{workflow.parameters.learn_rate}}
+--epochs={{workflow.parameters.epochs}}
+--train-ratio=1.0
+--eot='{{workflow.parameters.eot_token}}'
+--pad='{{workflow.parameters.pad_token}}'
+--warmup-ratio={{workflow.parameters.warmup_ratio}}
+--bs={{workflow.parameters.batch_size}}
+--bs-divisor={{workflow.parameters.batch_size_divisor}}
+--gradients={{workflow.parameters.gradients}}
+--zero-stage={{workflow.parameters.zero_stage}}
+--seed={{workflow.parameters.random_seed}}
+--output-path=/{{workflow.parameters.pvc}}/finetunes/
+--no-resume={{workflow.parameters.no_resume}}
+--cache=/{{workflow.parameters.pvc}}/cache/
+--save-steps={{workflow.parameters.save_steps}}
+--context-size={{workflow.parameters.context}}
+--project-id={{workflow.parameters.project_id}}
+--logs=/{{workflow.parameters.pvc}}/{{workflow.parameters.logs}}
+--fp16={{workflow.parameters.force_fp16}}
+--no-shuffle={{workflow.parameters.no_shuffle}}
+--prompt-file={{PROMPT_FILE}}
+--prompt-every={{workflow.parameters.prompt_every}}
+--prompt-tokens={{workflow.parameters.prompt_tokens}}
+--prompt-samples={{workflow.parameters.prompt_samples}}
+--top-k={{workflow.parameters.top_k}}
+--top-p={{workflow.parameters.top_p}}
+--temperature={{workflow.parameters.temperature}}
+--repetition-penalty={{workflow.parameters.repetition_penalty}}
+"""
+WORKFLOW_DEFAULTS = {"run_name": "my-run", "pvc": "finetune-data", "model": "EleutherAI/pythia-2.8b-deduped",
+                     "trust_remote_code": "false", "tensorizer_uri": "", "no_shuffle": "false", "eot_token": "",
+                     "pad_token": "", "context": "2048", "prompt_every": "0", "prompt_tokens": "200",
+                     "prompt_samples": "5", "top_k": "50", "top_p": "0.95", "temperature": "1.0",
+                     "repetition_penalty": "1.1", "warmup_ratio": "0.1", "batch_size": "-1", "force_fp16": "false",
+                     "batch_size_divisor": "1.0", "random_seed": "42", "learn_rate": "5e-5", "epochs": "1",
+                     "gradients": "5", "zero_stage": "3", "save_steps": "500", "no_resume": "false", "logs": "logs",
+                     "project_id": "huggingface"}
+
+
+def _workflow_argv(dataset_path, **overrides):
+    import re
+    import shlex
+    params = dict(WORKFLOW_DEFAULTS, **overrides)
+    text = WORKFLOW_FLAGS.replace("{{DATASET}}", dataset_path).replace("{{PROMPT_FILE}}", "")
+    text = re.sub(r"\{\{workflow\.parameters\.(\w+)\}\}", lambda m: params[m.group(1)], text)
+    return shlex.split(text) + ["--local_rank=0"]  # the DeepSpeed launcher appends this one (FT.py:261-266)
+
+
+def test_workflow_flag_string_parses_verbatim(tmp_path):
+    from decimal import Decimal
+    from kubernetes_cloud_b200.finetune import build_parser
+    ds = tmp_path / "dataset-EleutherAI_pythia_2_8b_deduped-2048-b-1-7c82f97.tokens"
+    ds.write_bytes(b"\0" * 4096)
+    a = build_parser().parse_args(_workflow_argv(str(ds)))
+    assert a.run_name == "my-run" and a.model == "/finetune-data/models/EleutherAI/pythia-2.8b-deduped"
+    assert a.dataset == str(ds) and a.trust_remote_code is False and a.tensorizer_uri == ""
+    assert a.lr == 5e-5 and a.epochs == 1 and a.train_ratio == Decimal("1.0") and a.warmup_ratio == Decimal("0.1")
+    assert a.bs == -1 and a.bs_divisor == Decimal("1.0") and a.gradients == 5 and a.zero_stage == 3 and a.seed == 42
+    assert a.resume is True and a.shuffle is True and a.fp16 is False and a.fp16_full_eval is False
+    assert a.save_steps == 500 and a.context_size == 2048 and a.prompt_file == "" and a.prompt_every == 0
+    assert a.top_p == 0.95 and a.repetition_penalty == 1.1 and a.local_rank == 0 and a.log_level == "INFO"
+    # the workflow's boolean parameters flipped: inverted-dest flags turn their destination off
+    b = build_parser().parse_args(_workflow_argv(str(ds), no_shuffle="true", no_resume="True", force_fp16="1",
+                                                 trust_remote_code="yes"))
+    assert b.shuffle is False and b.resume is False and b.fp16 is True and b.trust_remote_code is True
+
+
+def test_fuzzy_bool_grammar_and_validators(tmp_path):
+    from kubernetes_cloud_b200.finetune import build_parser
+    ds = tmp_path / "x.tokens"
+    ds.write_bytes(b"\0" * 64)
+    base = ["--run_name", "r", "--model", "gpt2", "--dataset", str(ds)]  # underscore aliases are accepted
+    parse = lambda *extra: build_parser().parse_args(base + list(extra))  # noqa: E731
+    assert parse().shuffle is True and parse().bs == -1 and parse().resume is True  # the reference's defaults
+    assert parse("--no-shuffle").shuffle is False                 # bare flag
+    for text in ("0", "no", "F", "False"):                        # "as if absent"
+        assert parse(f"--no-shuffle={text}").shuffle is True
+        assert parse(f"--fp16={text}").fp16 is False
+    for text in ("1", "true", "yes", "anything"):                 # "as if present"
+        assert parse(f"--no_shuffle={text}").shuffle is False
+        assert parse(f"--fp16={text}").fp16 is True
+    for bad in (["--bs=0"], ["--bs=-2"], ["--epochs=0"], ["--lr=-1"], ["--warmup-ratio=1.5"], ["--zero-stage=4"],
+                ["--seed=4294967296"], ["--dataset", str(tmp_path / "missing.tokens")], ["--log-level=loud"],
+                ["--prompt-every=-2"]):
+        with pytest.raises(SystemExit) as e:
+            parse(*bad)
+        assert e.value.code == 2  # argparse errors exit 2, as in the reference
+    assert parse("--log-level=debug").log_level == "DEBUG" and parse("--prompt-every=-1").prompt_every == -1
+
+
+def test_fp16_request_is_rejected_loudly(tmp_path):
+    from kubernetes_cloud_b200 import finetune
+    ds = tmp_path / "x.tokens"
+    ds.write_bytes(b"\0" * 64)
+    with pytest.raises(SystemExit) as e:
+        finetune.main(["--run-name", "r", "--model", "gpt2", "--dataset", str(ds), "--fp16"])
+    assert e.value.code == 1  # runtime failures exit 1 (FT.py:442-444)
