@@ -210,15 +210,23 @@ def main_gpu(args) -> None:
     local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    # SMs the last slab's dH GEMM leaves to the all-reduce of dW that runs beside it
-    sm_reserve = int(os.environ.get("FTK_BENCH_SM_RESERVE", "16")) if world > 1 else 0
     wire = os.environ.get("FTK_BENCH_WIRE", "fp32")  # fp32: the reference's communication_data_type; bf16: half the bytes
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-        if sm_reserve:
-            os.environ.setdefault("NCCL_MAX_CTAS", str(sm_reserve))  # the all-reduce must fit the reserved SMs
         dist.init_process_group("nccl", device_id=dev)
     L = _lib.lib()
+    # SMs the last slab's dH GEMM leaves to the all-reduce of dW that runs beside it: as many as one more
+    # wave of that GEMM frees (296 tiles = 4 waves on 74 SM pairs or 5 on 60, i.e. 28 SMs; under the power cap the
+    # GEMM's clock rises as it occupies fewer SMs, so the extra wave costs far less than 1/4).  NCCL keeps its own
+    # CTA count: capping it to the reserve (NCCL_MAX_CTAS) measured slower at 8 GPUs (profiles/r02_overlap_n8.txt).
+    sm_reserve = 0
+    if world > 1:
+        sms = torch.cuda.get_device_properties(dev).multi_processor_count
+        slab = L.ftk_lmhead_ce_fused_slab_rows(BATCH * CTX, D_MODEL, VOCAB, 0)
+        tiles = ((slab + 255) // 256) * ((D_MODEL + 255) // 256)
+        waves = -(-tiles // (sms // 2))
+        sm_reserve = max(0, min(32, sms - 2 * (-(-tiles // (waves + 1)))))
+        sm_reserve = int(os.environ.get("FTK_BENCH_SM_RESERVE", sm_reserve))
     stream = torch.cuda.current_stream(dev)
 
     # ---- synthetic inputs, resident in HBM (and a pinned host copy for the e2e leg)
@@ -370,6 +378,14 @@ def main_gpu(args) -> None:
         e[0] += 1
         e[1] += ms
     kern = {k: {"launches_per_step": v[0] / args.steps, "ms_per_step": v[1] / args.steps} for k, v in per_kernel.items()}
+    # how evenly the ranks' GPUs run the same kernels (under the power cap each GPU settles at its own clock): the
+    # step is paced by the slowest one, whatever the collective costs
+    own_ms = sum(v[1] for k, v in per_kernel.items() if k != "allreduce") / args.steps
+    rank_compute = [own_ms]
+    if world > 1:
+        t_all = [torch.zeros(1, device=dev, dtype=torch.float64) for _ in range(world)]
+        dist.all_gather(t_all, torch.tensor([own_ms], device=dev, dtype=torch.float64))
+        rank_compute = [float(x) for x in t_all]
 
     # ---- the same step without its parts, to price them (short loops)
     n_short = max(5, args.steps // 2)
@@ -517,7 +533,7 @@ def main_gpu(args) -> None:
                    "l2": "inputs (W 206 MB + H 67 MB) larger than the 126 MB L2; no explicit flush",
                    "grad_sync": (f"GradSync: ncclAllReduce(avg) of dW (103M {wire}) on the comm stream, started by the "
                                  f"dW-done event and running beside the last slab's dH GEMM, which leaves {sm_reserve} "
-                                 f"SMs to NCCL (NCCL_MAX_CTAS={sm_reserve}); the optimizer waits for it")
+                                 f"SMs free for it; the optimizer waits for it")
                    if world > 1 else "none (1 GPU)"},
         "tokens_per_s_per_gpu": value / world,
         "loss": loss_val,
@@ -565,6 +581,9 @@ def main_gpu(args) -> None:
         "clocks": clocks,
     }
     if world > 1:
+        line["rank_kernel_ms_per_step"] = {"min": min(rank_compute), "max": max(rank_compute),
+                                           "note": "sum of this library's kernels per step on each rank's GPU "
+                                                   "(all-reduce excluded); the slowest rank paces the step"}
         line["exposed_comm_ms_per_step"] = exposed_comm_ms
         line["allreduce_max_rel_err"] = allreduce_err
         line["full_gradient_allreduce"] = full_grad

@@ -33,10 +33,12 @@ from . import _lib
 
 
 class _Bucket:
-    __slots__ = ("flat", "params", "pending", "work")
+    __slots__ = ("flat", "params", "ready", "launched", "work")
 
     def __init__(self, flat: torch.Tensor, params: List[torch.nn.Parameter]):
-        self.flat, self.params, self.pending, self.work = flat, params, len(params), None
+        self.flat, self.params, self.work = flat, params, None
+        self.ready = set()      # ids of the parameters whose gradient is final in this optimizer step
+        self.launched = False   # the bucket's all-reduce has been issued in this optimizer step
 
 
 class GradSync:
@@ -122,29 +124,31 @@ class GradSync:
         if self.main_grads and p.grad is not None:
             p.main_grad.add_(p.grad)  # bf16 micro-batch gradient into the fp32 main gradient
             p.grad = None
+        self._note_ready(p, None)
+
+    def _note_ready(self, p: torch.nn.Parameter, after: Optional[torch.cuda.Event]) -> None:
         if not self.sync_now:
             return
         b = self._bucket_of[p]
-        b.pending -= 1
-        if b.pending == 0:
-            self._launch(b)
+        if b.launched or id(p) in b.ready:
+            return  # e.g. mark_ready() earlier in the step, then the autograd hook (it fires even for a None gradient)
+        b.ready.add(id(p))
+        if len(b.ready) == len(b.params):
+            self._launch(b, after)
 
     def mark_ready(self, p: torch.nn.Parameter, after: Optional[torch.cuda.Event] = None) -> None:
         """Tell the sync that ``p``'s gradient is final although no autograd hook will fire for it: the fused lm_head
         loss writes an untied ``lm_head.weight`` gradient into ``main_grad`` (or ``grad``) itself.  If that completes
         ``p``'s bucket, its all-reduce is launched now, and with ``after`` (the event given to
         ``ops.set_dw_done_event``) it waits for that event only, not for what the compute stream was given since:
-        the transfer then runs beside the dH GEMM.  Ignored inside ``no_sync()``."""
-        if not self.sync_now:
-            return
-        b = self._bucket_of[p]
-        b.pending -= 1
-        if b.pending == 0:
-            self._launch(b, after)
+        the transfer then runs beside the dH GEMM.  Ignored inside ``no_sync()``.  Only for parameters that receive
+        no further gradient in this step (not a tied ``wte``: the embedding's backward still adds to it)."""
+        self._note_ready(p, after)
 
     def _launch(self, b: _Bucket, after: Optional[torch.cuda.Event] = None) -> None:
         scale = (1.0 / self.world) if self.average else 1.0
         self.launched += 1
+        b.launched = True
         if self.backend == "ftk":
             dt = _lib.FTK_F32 if b.flat.dtype == torch.float32 else _lib.FTK_BF16
             if b.flat.dtype not in (torch.float32, torch.bfloat16):
@@ -178,7 +182,7 @@ class GradSync:
         (parameters without gradient this step) and makes the current stream wait for the communication stream.
         ``reduce=False`` only re-arms the buckets (a step measured without its communication)."""
         for b in self.buckets:
-            if b.pending != 0 and reduce:
+            if not b.launched and reduce:
                 self._launch(b)
         if self.backend == "ftk":
             stream = torch.cuda.current_stream(self.device).cuda_stream
@@ -189,7 +193,8 @@ class GradSync:
                     b.work.wait()
                     b.work = None
         for b in self.buckets:
-            b.pending = len(b.params)
+            b.ready.clear()
+            b.launched = False
 
     def zero_grad(self) -> None:
         """Zero the flat buckets (keeps every ``param.grad`` a view; do not use ``set_to_none=True``)."""

@@ -46,22 +46,29 @@ if os.path.exists(rep):
             "lts__throughput.avg.pct_of_peak_sustained_elapsed", "l1tex__m_xbar2l1tex_read_bytes.sum",
             "sm__warps_active.avg.pct_of_peak_sustained_active", "launch__registers_per_thread",
             "sm__cycles_elapsed.avg.per_second", "launch__grid_size", "launch__block_size",
-            "launch__shared_mem_per_block_dynamic", "launch__cluster_dim_x",
-            "sm__ops_path_tensor_op_hmma_src_bf16_dst_fp32_sparsity_off.sum.pct_of_peak_sustained_elapsed"]
+            "launch__shared_mem_per_block_dynamic", "launch__cluster_dim_x"]
     ix = {k: hdr.index(k) for k in keys if k in hdr}
     ni = hdr.index("Kernel Name")
-    traffic = {}
+    scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}
+
+    def kind(name: str) -> str:
+        for pat, k in (("FwdKeepEpi", "fwd_keep"), ("FwdEpi", "fwd"), ("DzEpi", "dz"), (", 0, 1,", "dH"), (", 1, 1,", "dW"),
+                       ("probs_to_dz", "convert"), ("gather_windows", "gather")):
+            if pat in name:
+                return k
+        return name[:30]
+
+    traffic = collections.OrderedDict()
     with open(os.path.join(out_dir, f"{tag}_ncu_full_summary.txt"), "w") as f:
-        f.write("# ncu --set full --clock-control none --import-source on (one launch of each kernel, under the profiler)\n")
+        f.write("# ncu --set full --clock-control none --import-source on (consecutive launches of one step, under the profiler)\n")
         for row in rows[2:]:
-            f.write(f"\n{row[ni][:150]}\n")
+            f.write(f"\n[{kind(row[ni])}] {row[ni][:150]}\n")
             for k, i in ix.items():
                 f.write(f"    {k} [{units[i]}] = {row[i]}\n")
-            name = row[ni]
-            rd = float(row[ix["dram__bytes_read.sum"]]) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}[units[ix["dram__bytes_read.sum"]]]
-            wr = float(row[ix["dram__bytes_write.sum"]]) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1}[units[ix["dram__bytes_write.sum"]]]
-            key = "fwd" if "FwdEpi" in name else "dz" if "DzEpi" in name else "dh" if ", 0, 1," in name else "dw" if ", 1, 1," in name else name[:30]
-            traffic[f"{key}_dram_bytes_per_launch"] = rd + wr
+            rd = float(row[ix["dram__bytes_read.sum"]]) * scale[units[ix["dram__bytes_read.sum"]]]
+            wr = float(row[ix["dram__bytes_write.sum"]]) * scale[units[ix["dram__bytes_write.sum"]]]
+            key = f"{kind(row[ni])}_dram_bytes_per_step"  # summed over that kernel's launches in the captured step
+            traffic[key] = traffic.get(key, 0.0) + rd + wr
     json.dump(traffic, open(os.path.join(out_dir, "traffic.json"), "w"), indent=1)
     print(open(os.path.join(out_dir, f"{tag}_ncu_full_summary.txt")).read())
     print(traffic)
