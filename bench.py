@@ -372,6 +372,20 @@ def main_gpu(args) -> None:
     ms_step = ms_total / args.steps
     value = world * M * args.steps / (ms_total / 1e3)
     loss_val = float(loss)
+    # span of the fused forward+backward inside each step: first sweep start -> last gradient GEMM end (the
+    # conversion passes run on the side stream beside the sweeps, so summing kernel durations would double count)
+    spans, cur0, cur1 = [], None, None
+    for name, ms, st_ in trace:
+        if name == "gather":
+            if cur0 is not None:
+                spans.append(cur1 - cur0)
+            cur0, cur1 = None, None
+        elif name in ("fwd_keep", "fwd", "dz", "convert", "dH", "dW"):
+            cur0 = st_ if cur0 is None else min(cur0, st_)
+            cur1 = st_ + ms if cur1 is None else max(cur1, st_ + ms)
+    if cur0 is not None:
+        spans.append(cur1 - cur0)
+    fused_span_ms = sum(spans) / max(len(spans), 1)
     per_kernel = {}
     for name, ms in timeline:
         e = per_kernel.setdefault(name, [0, 0.0])
@@ -520,7 +534,7 @@ def main_gpu(args) -> None:
     tp = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tp):
         traffic = json.load(open(tp)).get(f"{dom}_dram_bytes_per_step")
-    fused_ms = sum(tensor_ms.values()) + kern.get("convert", {}).get("ms_per_step", 0.0)
+    fused_ms = fused_span_ms
     conv = kern.get("convert")
     line = {
         "metric": "tokens/s", "value": value, "unit": "tokens/s", "n_gpus": world, "steps": args.steps,
@@ -552,8 +566,10 @@ def main_gpu(args) -> None:
                            "frac_of_burst": 3 * flops_gemm / (fused_ms / 1e3) / 1e12 / peaks["burst"],
                            "frac_of_nominal_2250": 3 * flops_gemm / (fused_ms / 1e3) / 1e12 / 2250.0,
                            "ms": fused_ms,
-                           "note": "algorithmic 6MVd over the kernels of the fused forward+backward (no recompute: "
-                                   "executed = algorithmic)"},
+                           "note": "algorithmic 6MVd over the span of the fused forward+backward call inside the step "
+                                   "(first sweep start to last gradient GEMM end, from the launch timeline; no "
+                                   "recompute: executed = algorithmic; the conversion passes run on a side stream "
+                                   "beside the sweeps, which is why the per-kernel times overlap)"},
         "roofline_convert": ({"bound": "hbm", "achieved": 4.0 * M * ((VOCAB + 63) // 64 * 64) / (conv["ms_per_step"] / 1e3) / 1e9,
                               "peak": peaks["hbm"], "unit": "GB/s", "ms_per_step": conv["ms_per_step"],
                               "note": "bf16 numerators -> dZ in place: 2 B read + 2 B written per (token, vocab) entry"}

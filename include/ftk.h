@@ -223,7 +223,9 @@ int ftk_lmhead_ce_bwd(const void* H, const void* W, const void* bias, const int6
  * keeping anything of size [tokens x vocab] between forward and backward: the rows are processed in slabs, and for
  * each slab the forward sweep leaves bf16 softmax numerators in the workspace, a finalize pass gives lse, one
  * HBM-bound pass turns the numerators into dZ in place, and the dH and dW GEMMs consume them before the next slab
- * overwrites them. The numerators slab is capped at 1 GiB whatever M is (at most 10,496 rows at V = 50,257);
+ * overwrites them. With two or more slabs there are two slab buffers, and the conversion of one slab runs on a
+ * library-owned side stream (joined back into `stream` before the call's last kernels) while the next slab's sweep
+ * fills the other. A slab is capped at 1 GiB whatever M is (at most 10,496 rows at V = 50,257; workspace <= 2.1 GiB);
  * ftk_lmhead_ce_fused_slab_rows reports the rows per slab the library would pick (slab_rows = 0) or clamps a
  * request.
  *

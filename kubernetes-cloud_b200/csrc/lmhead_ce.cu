@@ -14,6 +14,8 @@
 // Three mbarrier pipelines: smem full/empty (TMA <-> MMA), TMEM full/empty (MMA <-> epilogue).
 #include <cuda.h>
 #include <math.h>
+
+#include <mutex>
 #include <stdlib.h>
 #include <string.h>
 
@@ -794,8 +796,10 @@ __global__ void __launch_bounds__(128) dbias_kernel(const __nv_bfloat16* __restr
 
 
 // Kept numerators -> dZ in place: dZ[r, c] = e[r, c] * exp(cref[tile(c)][r] - lse[r]) * scale_r - (c == target_r) * scale_r,
-// scale_r = 0 on ignored rows.  HBM-bound.  One block per row: the per-tile factors of the row go to shared memory
-// once, then the row streams through in 16-byte accesses, four independent loads per thread in flight.
+// scale_r = 0 on ignored rows.  HBM-bound.  One block per row, 16-byte accesses, four independent loads per thread in
+// flight; the per-tile factor is recomputed per vector (32 consecutive lanes share a tile: one broadcast load of cref
+// and one MUFU per 8 elements).  No shared memory and 40 registers, so its blocks fit on SMs whose shared memory is
+// almost entirely held by a persistent GEMM CTA: the fused path runs it on a second stream beside the next slab's sweep.
 __global__ void __launch_bounds__(256) probs_to_dz_kernel(__nv_bfloat16* __restrict__ probs,
                                                           const float* __restrict__ cref,
                                                           const float* __restrict__ lse,
@@ -803,7 +807,6 @@ __global__ void __launch_bounds__(256) probs_to_dz_kernel(__nv_bfloat16* __restr
                                                           int Mpad, int n_tiles, float scale,
                                                           const float* __restrict__ scale_dev,
                                                           const int32_t* __restrict__ nvalid_dev) {
-  extern __shared__ float s_f[];  // n_tiles factors
   const int r = blockIdx.x;
   if (r >= rows) return;
   const int tgt = static_cast<int>(targets[r]);
@@ -811,31 +814,33 @@ __global__ void __launch_bounds__(256) probs_to_dz_kernel(__nv_bfloat16* __restr
   if (scale_dev != nullptr) sc *= __ldg(scale_dev);
   if (nvalid_dev != nullptr) sc /= static_cast<float>(__ldg(nvalid_dev));
   if (tgt < 0) sc = 0.f;
-  const float l = __ldg(lse + r);
-  for (int t = threadIdx.x; t < n_tiles; t += 256)
-    s_f[t] = exp2f((__ldg(cref + static_cast<size_t>(t) * Mpad + r) - l) * kLog2e) * sc;
-  __syncthreads();
+  const float l2 = -__ldg(lse + r) * kLog2e;
+  const float* cr = cref + r;
   uint4* row = reinterpret_cast<uint4*>(probs + static_cast<size_t>(r) * ld);
   const int nvec = ld / 8;  // ld is a multiple of 64
   for (int i0 = threadIdx.x; i0 < nvec; i0 += 256 * 4) {
     uint4 in[4];
+    float f[4];
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int i = i0 + u * 256;
-      if (i < nvec) in[u] = __ldcs(row + i);
+      if (i < nvec) {
+        in[u] = __ldcs(row + i);
+        const int t = min((i * 8) >> 8, n_tiles - 1);  // 256-column tiles; pad columns past V reuse the last tile
+        f[u] = fast_exp2(fmaf(__ldg(cr + static_cast<size_t>(t) * Mpad), kLog2e, l2)) * sc;
+      }
     }
 #pragma unroll
     for (int u = 0; u < 4; ++u) {
       const int i = i0 + u * 256;
       if (i >= nvec) break;
       const int c8 = i * 8;
-      const float f = s_f[c8 >> 8];  // 256-column tiles
       const uint32_t iw[4] = {in[u].x, in[u].y, in[u].z, in[u].w};
       uint32_t ow[4];
 #pragma unroll
       for (int e = 0; e < 4; ++e) {
         const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&iw[e]);
-        float a = __low2float(h) * f, b = __high2float(h) * f;
+        float a = __low2float(h) * f[u], b = __high2float(h) * f[u];
         if (c8 + 2 * e == tgt) a -= sc;
         if (c8 + 2 * e + 1 == tgt) b -= sc;
         ow[e] = pack_bf16x2(a, b);
@@ -1403,7 +1408,7 @@ extern "C" int ftk_lmhead_ce_bwd_kept(const void* H, const void* W, const int64_
   {
     const int n_tiles = ceil_div(V, 256);
     ftk::TimelineScope tl_(FTK_TL_CONVERT, st);
-    probs_to_dz_kernel<<<static_cast<unsigned>(M), 256, n_tiles * sizeof(float), st>>>(
+    probs_to_dz_kernel<<<static_cast<unsigned>(M), 256, 0, st>>>(
         static_cast<__nv_bfloat16*>(probs), cref, lse, targets, static_cast<int>(M), V, static_cast<int>(ld),
         static_cast<int>(round_up(M, 256)), n_tiles, grad_scale, grad_scale_dev, n_valid_dev);
     FTK_CUDA_CHECK(cudaGetLastError());
@@ -1419,7 +1424,7 @@ extern "C" int ftk_lmhead_ce_bwd_kept(const void* H, const void* W, const int64_
 // Forward and backward in one call, with a bounded numerators slab (ftk.h: ftk_lmhead_ce_fused).
 namespace {
 
-constexpr size_t kFusedSlabBudget = size_t(1) << 30;  // bytes of bf16 numerators alive at any moment
+constexpr size_t kFusedSlabBudget = size_t(1) << 30;  // bytes of one bf16 numerators slab; two are alive at a time
 
 // Charged time of the forward sweep and the dH GEMM over `r` rows, in 256 x 256 x 64 MMA blocks per SM pair: whole
 // waves over the SM pairs, so a launch that needs 3.46 waves is charged 4.
@@ -1456,6 +1461,9 @@ int64_t plan_fused_slab(int64_t M, int d, int V, int sm_count, int kCG) {
     // each extra slab re-reads and re-writes dW once: about V * d * 8 bytes of HBM traffic, charged as tensor time
     // at ~100 flop per byte (it overlaps the dW GEMM)
     cost += (n_full + (rem > 0) - 1) * (static_cast<int64_t>(V) * d * 8 * 100 / (2ll * 256 * 256 * 64)) / n_groups;
+    // a single slab has no other slab's sweep to hide its conversion pass behind: 4 bytes of HBM traffic per
+    // (row, column) at ~6.2 TB/s, in units of the 0.45 us one SM pair takes for a 256 x 256 x 64 block
+    if (n_full + (rem > 0) == 1) cost += static_cast<int64_t>(static_cast<double>(M) * ld * 1.45e-6);
     if (cost < best_cost) {
       best_cost = cost;
       best_rows = rows;
@@ -1466,27 +1474,52 @@ int64_t plan_fused_slab(int64_t M, int d, int V, int sm_count, int kCG) {
 
 struct FusedWorkspace {
   void* fwd;
-  float* cref;
-  __nv_bfloat16* probs;
+  float* cref[2];
+  __nv_bfloat16* probs[2];
   int64_t slab;
+  int n_buf;
   size_t fwd_bytes, bytes;
 };
 
+// One set of forward statistics (a slab's finalize has run before the next sweep starts), and a numerators slab plus
+// its reference-maxima table per buffer: two buffers when the rows make two or more slabs, so that the conversion of
+// one slab can run on the side stream while the next slab's sweep fills the other.
 FusedWorkspace carve_fused(void* base, int64_t M, int V, int64_t slab) {
   FusedWorkspace w;
   if (slab > M) slab = M;
   w.slab = slab;
+  w.n_buf = (M > slab) ? 2 : 1;
   const uintptr_t p = reinterpret_cast<uintptr_t>(base);
   size_t off = 0;
   w.fwd = reinterpret_cast<void*>(p + off);
   w.fwd_bytes = carve_fwd(nullptr, slab).bytes;
   off += round_up(w.fwd_bytes, 256);
-  w.cref = reinterpret_cast<float*>(p + off);
-  off += round_up(static_cast<size_t>(ceil_div(V, 256)) * round_up(slab, 256) * sizeof(float), 256);
-  w.probs = reinterpret_cast<__nv_bfloat16*>(p + off);
-  off += static_cast<size_t>(round_up(slab, 256)) * dz_pitch(V) * 2;
+  for (int b = 0; b < 2; ++b) {
+    if (b >= w.n_buf) {
+      w.cref[b] = w.cref[0];
+      w.probs[b] = w.probs[0];
+      continue;
+    }
+    w.cref[b] = reinterpret_cast<float*>(p + off);
+    off += round_up(static_cast<size_t>(ceil_div(V, 256)) * round_up(slab, 256) * sizeof(float), 256);
+    w.probs[b] = reinterpret_cast<__nv_bfloat16*>(p + off);
+    off += static_cast<size_t>(round_up(slab, 256)) * dz_pitch(V) * 2;
+  }
   w.bytes = off;
   return w;
+}
+
+// The side stream the conversion passes run on: one per device, created on first use and kept.
+int fused_side_stream(cudaStream_t* out) {
+  static cudaStream_t streams[64] = {nullptr};
+  static std::mutex mu;
+  int dev = 0;
+  FTK_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return ftk::fail(FTK_EINVAL, "device ordinal %d out of range", dev);
+  std::lock_guard<std::mutex> lk(mu);
+  if (streams[dev] == nullptr) FTK_CUDA_CHECK(cudaStreamCreateWithFlags(&streams[dev], cudaStreamNonBlocking));
+  *out = streams[dev];
+  return FTK_OK;
 }
 
 int fused_slab_rows(int64_t M, int d, int V, int64_t slab_rows, int64_t* out) {
@@ -1546,41 +1579,97 @@ extern "C" int ftk_lmhead_ce_fused(const void* H, const void* W, const void* bia
   const int n_tiles = ceil_div(V, 256);
   // Slabs: the remainder (M mod slab rows) first, full slabs after it, so the last slab -- the one whose dH GEMM a
   // data-parallel caller overlaps with the all-reduce of dW -- is a full one.
+  // Schedule, with two slab buffers: sweep(0), sweep(1), dH(0), dW(0), sweep(2), dH(1), dW(1), ... on `stream`, and
+  // convert(i) on the side stream between sweep(i) and dH(i), i.e. beside sweep(i+1) (or beside the gradient GEMMs of
+  // slab i-1 for the last one).  The conversion is HBM-bound and shared-memory free, the sweeps are tensor-bound and
+  // hold the shared memory: they share the SMs.  With one slab everything is in stream order.
   const int64_t rem = M % fw.slab;
-  bool first = true;
-  for (int64_t r0 = 0; r0 < M;) {
-    const int64_t rows = (r0 == 0 && rem != 0) ? rem : fw.slab;
-    const void* Hs = static_cast<const uint8_t*>(H) + static_cast<size_t>(r0) * d * 2;
-    void* dHs = static_cast<uint8_t*>(dH) + static_cast<size_t>(r0) * d * 2;
-    const FwdWorkspace ws = carve_fwd(fw.fwd, rows);
-    // (1) logits tile by tile: softmax statistics + bf16 numerators of this slab; (2) lse and the slab's loss
-    int rc = pair ? run_fwd_keep<2>(Hs, W, bias, targets + r0, rows, d, V, lse + r0, loss_sum, nullptr, fw.probs,
-                                    fw.cref, ws, di.sm_count, st, 1, 0)
-                  : run_fwd_keep<1>(Hs, W, bias, targets + r0, rows, d, V, lse + r0, loss_sum, nullptr, fw.probs,
-                                    fw.cref, ws, di.sm_count, st, 1, 0);
+  const int n_slabs = static_cast<int>(M / fw.slab + (rem != 0));
+  cudaStream_t side = st;
+  cudaEvent_t ev_swept[2] = {nullptr, nullptr}, ev_conv[2] = {nullptr, nullptr};
+  const bool overlap = fw.n_buf == 2 && n_slabs >= 2;
+  auto cleanup = [&]() {
+    for (int b = 0; b < 2; ++b) {
+      if (ev_swept[b] != nullptr) cudaEventDestroy(ev_swept[b]);  // pending work keeps what it needs
+      if (ev_conv[b] != nullptr) cudaEventDestroy(ev_conv[b]);
+    }
+  };
+  if (overlap) {
+    if (int rc = fused_side_stream(&side)) return rc;
+    for (int b = 0; b < 2; ++b) {
+      cudaError_t e = cudaEventCreateWithFlags(&ev_swept[b], cudaEventDisableTiming);
+      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev_conv[b], cudaEventDisableTiming);
+      if (e != cudaSuccess) {
+        cleanup();
+        return ftk::fail(FTK_ECUDA, "ftk_lmhead_ce_fused: cudaEventCreate failed: %s", cudaGetErrorString(e));
+      }
+    }
+  }
+  struct Slab {
+    int64_t r0, rows;
+  };
+  auto slab_at = [&](int i) {
+    Slab sl;
+    if (rem != 0) {
+      sl.r0 = (i == 0) ? 0 : rem + static_cast<int64_t>(i - 1) * fw.slab;
+      sl.rows = (i == 0) ? rem : fw.slab;
+    } else {
+      sl.r0 = static_cast<int64_t>(i) * fw.slab;
+      sl.rows = fw.slab;
+    }
+    return sl;
+  };
+  // (1) logits tile by tile: softmax statistics + bf16 numerators of slab i; (2) lse and the slab's loss;
+  // (3) numerators -> dZ in place, on the side stream
+  auto sweep_and_convert = [&](int i) -> int {
+    const Slab sl = slab_at(i);
+    const int b = i & (fw.n_buf - 1);
+    const void* Hs = static_cast<const uint8_t*>(H) + static_cast<size_t>(sl.r0) * d * 2;
+    const FwdWorkspace ws = carve_fwd(fw.fwd, sl.rows);
+    int rc = pair ? run_fwd_keep<2>(Hs, W, bias, targets + sl.r0, sl.rows, d, V, lse + sl.r0, loss_sum, nullptr,
+                                    fw.probs[b], fw.cref[b], ws, di.sm_count, st, 1, 0)
+                  : run_fwd_keep<1>(Hs, W, bias, targets + sl.r0, sl.rows, d, V, lse + sl.r0, loss_sum, nullptr,
+                                    fw.probs[b], fw.cref[b], ws, di.sm_count, st, 1, 0);
     if (rc) return rc;
-    // (3) numerators -> dZ in place
+    if (overlap) {
+      FTK_CUDA_CHECK(cudaEventRecord(ev_swept[b], st));
+      FTK_CUDA_CHECK(cudaStreamWaitEvent(side, ev_swept[b], 0));
+    }
     {
-      ftk::TimelineScope tl_(FTK_TL_CONVERT, st);
-      probs_to_dz_kernel<<<static_cast<unsigned>(rows), 256, n_tiles * sizeof(float), st>>>(
-          fw.probs, fw.cref, lse + r0, targets + r0, static_cast<int>(rows), V, static_cast<int>(ld),
-          static_cast<int>(round_up(rows, 256)), n_tiles, grad_scale, grad_scale_dev, n_valid);
+      ftk::TimelineScope tl_(FTK_TL_CONVERT, side);
+      probs_to_dz_kernel<<<static_cast<unsigned>(sl.rows), 256, 0, side>>>(
+          fw.probs[b], fw.cref[b], lse + sl.r0, targets + sl.r0, static_cast<int>(sl.rows), V, static_cast<int>(ld),
+          static_cast<int>(round_up(sl.rows, 256)), n_tiles, grad_scale, grad_scale_dev, n_valid);
       FTK_CUDA_CHECK(cudaGetLastError());
     }
-    // (4) dH of these rows, dW accumulated over the slabs
-    const int acc = (accumulate || !first) ? 1 : 0;
-    const bool last = r0 + rows >= M;
+    if (overlap) FTK_CUDA_CHECK(cudaEventRecord(ev_conv[b], side));
+    return FTK_OK;
+  };
+  // (4) dH of slab i's rows, dW accumulated over the slabs
+  auto grad_gemms = [&](int i) -> int {
+    const Slab sl = slab_at(i);
+    const int b = i & (fw.n_buf - 1);
+    if (overlap) FTK_CUDA_CHECK(cudaStreamWaitEvent(st, ev_conv[b], 0));
+    const void* Hs = static_cast<const uint8_t*>(H) + static_cast<size_t>(sl.r0) * d * 2;
+    void* dHs = static_cast<uint8_t*>(dH) + static_cast<size_t>(sl.r0) * d * 2;
+    const int acc = (accumulate || i > 0) ? 1 : 0;
     GradGemmPlan plan;
-    plan.overlap_tail = last && dw_done_event != nullptr;
+    plan.overlap_tail = (i == n_slabs - 1) && dw_done_event != nullptr;
     plan.full_sms = !plan.overlap_tail;  // the SM reserve only matters where a collective can run beside us
     plan.dw_done = static_cast<cudaEvent_t>(dw_done_event);
-    rc = pair ? run_grad_gemms<2>(Hs, W, rows, d, V, dHs, dW, dw_dtype, acc, dbias, fw.probs, di.sm_count, st, plan)
-              : run_grad_gemms<1>(Hs, W, rows, d, V, dHs, dW, dw_dtype, acc, dbias, fw.probs, di.sm_count, st, plan);
-    if (rc) return rc;
-    r0 += rows;
-    first = false;
+    return pair ? run_grad_gemms<2>(Hs, W, sl.rows, d, V, dHs, dW, dw_dtype, acc, dbias, fw.probs[b], di.sm_count, st,
+                                    plan)
+                : run_grad_gemms<1>(Hs, W, sl.rows, d, V, dHs, dW, dw_dtype, acc, dbias, fw.probs[b], di.sm_count, st,
+                                    plan);
+  };
+  int rc = sweep_and_convert(0);
+  for (int i = 0; i < n_slabs && rc == FTK_OK; ++i) {
+    if (overlap && i + 1 < n_slabs) rc = sweep_and_convert(i + 1);  // fills the other buffer while convert(i) runs
+    if (rc == FTK_OK) rc = grad_gemms(i);
+    if (!overlap && rc == FTK_OK && i + 1 < n_slabs) rc = sweep_and_convert(i + 1);
   }
-  return FTK_OK;
+  cleanup();
+  return rc;
 }
 
 extern "C" int ftk_scale_unless_one(void* buf, size_t n, int32_t dtype, const float* factor_dev, int32_t poison,
