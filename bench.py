@@ -298,7 +298,7 @@ def main_gpu(args) -> None:
         return 19.0 * n_bulk * CTX / (g0.elapsed_time(g1) / 10 / 1e3) / 1e9
 
     gather_gbs = bulk_gather_gbs()
-    _lib.set_option("gather_variant", 1 - int(os.environ.get("FTK_BENCH_GATHER_DEFAULT_DIRECT", "0")))
+    _lib.set_option("gather_variant", 2)  # the shared-memory staged kernel (the default for small batches)
     gather_other_gbs = bulk_gather_gbs()
     _lib.set_option("gather_variant", 0)
     _lib.set_option("gather_stores", 2)
@@ -323,7 +323,7 @@ def main_gpu(args) -> None:
 
     def step(hidden: torch.Tensor, tok: torch.Tensor, idx: torch.Tensor, comm: bool = True, optimizer: bool = True):
         ids, targets, mask, n_valid_rows = torch.ops.ftk.gather_windows(tok, idx, CTX, PAD_ID, True, True)
-        sync.zero_grad()
+        sync.zero_grad(overwritten_by_fused_loss=W)  # W's gradient is overwritten by the first slab, not zeroed + added
         h = hidden.detach().requires_grad_(True)
         loss = ops.fused_lmhead_ce(h, W, None, targets.view(-1))  # dH, dW (into W's gradient bucket) made here
         early = fused_mode[0] and world > 1 and comm
@@ -578,7 +578,7 @@ def main_gpu(args) -> None:
                             "frac": gather_gbs / peaks["hbm"],
                             "note": "bulk launch of 2^26 tokens drawn once each from a 134 MB source (> L2), 19 B/token, "
                                     "streaming stores, timed through the C ABI",
-                            "other_variant_gbs": gather_other_gbs, "plain_stores_gbs": gather_plain_gbs},
+                            "staged_variant_gbs": gather_other_gbs, "plain_stores_gbs": gather_plain_gbs},
         "roofline_adamw": ({"bound": "hbm",
                             "achieved": ((32.0 if wire == "fp32" else 28.0) * VOCAB * D_MODEL) / (kern["adamw"]["ms_per_step"] / 1e3) / 1e9,
                             "peak": peaks["hbm"], "unit": "GB/s", "ms_per_step": kern["adamw"]["ms_per_step"],

@@ -54,7 +54,8 @@ const char* ftk_last_error(void);
  * Process-wide tuning options. Each is one atomic integer read at launch time; nothing is read from the
  * environment. No counterpart in the reference.
  *   FTK_OPT_CTA_GROUP       2 (default): tcgen05 cta_group::2, a CTA pair shares one 256-row tile; 1: single CTAs
- *   FTK_OPT_GATHER_VARIANT  0 (default): pick by shape; 1: the direct (no shared memory) kernel where it applies
+ *   FTK_OPT_GATHER_VARIANT  0 (default): pick by shape and size; 1: the direct (no shared memory) kernel where it
+ *                           applies; 2: the shared-memory staged kernel where it applies
  *   FTK_OPT_GATHER_STORES   0 (default): streaming stores for launches of >= 4 M tokens; 1: always; 2: never
  *   FTK_OPT_SM_RESERVE      n in [0, 64]: SMs the persistent lm_head kernels launched from now on leave idle
  *                           (same as ftk_set_sm_reserve)
@@ -248,6 +249,8 @@ int ftk_lmhead_ce_bwd(const void* H, const void* W, const void* bias, const int6
  * rescaled: a wrong assumption then shows instead of passing silently).
  */
 int64_t ftk_lmhead_ce_fused_slab_rows(int64_t M, int32_t d, int32_t V, int64_t slab_rows);
+/* The slab planner on its own: rows per slab for a device with `sm_count` SMs (no device needed; host logic tests). */
+int64_t ftk_lmhead_ce_fused_plan(int64_t M, int32_t d, int32_t V, int32_t sm_count, int32_t cta_group);
 size_t ftk_lmhead_ce_fused_workspace(int64_t M, int32_t d, int32_t V, int64_t slab_rows);
 int ftk_lmhead_ce_fused(const void* H, const void* W, const void* bias, const int64_t* targets, int64_t M, int32_t d,
                         int32_t V, float grad_scale, const float* grad_scale_dev, float* lse, float* loss_sum,

@@ -35,6 +35,7 @@ SIGNATURES = {
     "ftk_lmhead_ce_fwd_static": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p,
                                            c_void_p, c_void_p, c_void_p]),
     "ftk_lmhead_ce_fused_slab_rows": (c_int64, [c_int64, c_int32, c_int32, c_int64]),
+    "ftk_lmhead_ce_fused_plan": (c_int64, [c_int64, c_int32, c_int32, c_int32, c_int32]),
     "ftk_lmhead_ce_fused_workspace": (c_size_t, [c_int64, c_int32, c_int32, c_int64]),
     "ftk_lmhead_ce_fused": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_float,
                                       c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int32,
@@ -108,7 +109,7 @@ def check(rc: int, what: str) -> None:
 
 
 def set_option(name: str, value: int) -> None:
-    """ftk_set_option by name: "cta_group" (1|2), "gather_variant" (0 auto|1 direct), "gather_stores"
+    """ftk_set_option by name: "cta_group" (1|2), "gather_variant" (0 auto|1 direct|2 staged), "gather_stores"
     (0 auto|1 streaming|2 plain), "sm_reserve" (0..64)."""
     check(lib().ftk_set_option(OPTIONS[name], int(value)), f"ftk_set_option({name})")
 

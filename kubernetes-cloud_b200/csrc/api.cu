@@ -76,7 +76,8 @@ extern "C" int ftk_set_option(int32_t key, int32_t value) {
       FTK_REQUIRE(value == 1 || value == 2, "ftk_set_option: cta_group must be 1 or 2, got %d", value);
       break;
     case FTK_OPT_GATHER_VARIANT:
-      FTK_REQUIRE(value == 0 || value == 1, "ftk_set_option: gather variant must be 0 (auto) or 1 (direct), got %d", value);
+      FTK_REQUIRE(value >= 0 && value <= 2, "ftk_set_option: gather variant must be 0 (auto), 1 (direct) or 2 (staged), got %d",
+                  value);
       break;
     case FTK_OPT_GATHER_STORES:
       FTK_REQUIRE(value >= 0 && value <= 2, "ftk_set_option: gather stores must be 0 (auto), 1 (streaming) or 2 (plain), got %d",

@@ -1437,6 +1437,12 @@ int64_t slab_cost(int64_t r, int d, int V, int n_groups, int kCG) {
   const int64_t w128 = ceil_div(static_cast<int64_t>(n_mblk) * ceil_div(d, 128), n_groups);
   const int64_t w = (w128 * kNarrowTilePenaltyPct < w256 * 100) ? (w128 * kNarrowTilePenaltyPct + 99) / 100 : w256;
   cost += w * ceil_div(V, 64) / 2;
+  // dW: K = the slab's rows.  The work is the same whatever the split, but a 256 x 256 output tile's epilogue
+  // (TMEM read, read-modify-write of dW) takes about as long as 48 K blocks of MMAs, so slabs under ~3,000 rows make
+  // the dW GEMM epilogue-paced (measured: 4,096 rows as 2 x 2,048 is 30 % slower than as one slab).
+  const int64_t k_dw = ceil_div(r, 64);
+  cost += static_cast<int64_t>(ceil_div(static_cast<int64_t>(ceil_div(V, BM * kCG)) * ceil_div(d, 256), n_groups)) *
+          (k_dw > 48 ? k_dw : 48);
   return cost;
 }
 
@@ -1537,6 +1543,11 @@ extern "C" int64_t ftk_lmhead_ce_fused_slab_rows(int64_t M, int32_t d, int32_t V
   int64_t slab = 0;
   if (M <= 0 || d <= 0 || V <= 0 || fused_slab_rows(M, d, V, slab_rows, &slab)) return 0;
   return slab;
+}
+
+extern "C" int64_t ftk_lmhead_ce_fused_plan(int64_t M, int32_t d, int32_t V, int32_t sm_count, int32_t cta_group) {
+  if (M <= 0 || d <= 0 || V <= 0 || sm_count <= 0 || (cta_group != 1 && cta_group != 2)) return 0;
+  return plan_fused_slab(M, d, V, sm_count, cta_group);
 }
 
 extern "C" size_t ftk_lmhead_ce_fused_workspace(int64_t M, int32_t d, int32_t V, int64_t slab_rows) {

@@ -196,10 +196,26 @@ class GradSync:
             b.ready.clear()
             b.launched = False
 
-    def zero_grad(self) -> None:
-        """Zero the flat buckets (keeps every ``param.grad`` a view; do not use ``set_to_none=True``)."""
+    def zero_grad(self, overwritten_by_fused_loss: Optional[torch.nn.Parameter] = None) -> None:
+        """Zero the flat buckets (keeps every ``param.grad`` a view; do not use ``set_to_none=True``).
+        ``overwritten_by_fused_loss``: the lm_head weight whose gradient the fused loss writes first in every step
+        (before the embedding's backward of a tied ``wte``, before anything else touches it).  Its part of the bucket
+        is not zeroed; the gradient tensor is marked so that the next fused call overwrites it instead of adding
+        (412 MB less to write and 412 MB less to read per step for a 103 M-element fp32 main gradient)."""
+        skip = overwritten_by_fused_loss
         for b in self.buckets:
-            b.flat.zero_()
+            if skip is not None and any(p is skip for p in b.params):
+                tgt = skip.main_grad if self.main_grads else skip.grad
+                lo = tgt.data_ptr() - b.flat.data_ptr()
+                lo //= b.flat.element_size()
+                hi = lo + tgt.numel()
+                if lo > 0:
+                    b.flat[:lo].zero_()
+                if hi < b.flat.numel():
+                    b.flat[hi:].zero_()
+                tgt._ftk_overwrite = True
+            else:
+                b.flat.zero_()
 
     def close(self) -> None:
         if self._handle is not None:

@@ -126,14 +126,19 @@ def set_bwd_slab_rows(rows: int) -> None:
 
 
 def _dw_target(W: torch.Tensor, dw_fp32: bool, dW_into: Optional[torch.Tensor]):
-    """(tensor the dW GEMM writes, dtype code, accumulate flag)."""
+    """(tensor the dW GEMM writes, dtype code, accumulate flag).  A target marked ``_ftk_overwrite`` (GradSync's lazy
+    ``zero_grad``) is overwritten instead of added to, once: the zeroing pass and the first read of it are saved."""
     if dW_into is None:
         dW = torch.empty(W.shape, dtype=torch.float32 if dw_fp32 else torch.bfloat16, device=W.device)
         return dW, (_lib.FTK_F32 if dw_fp32 else _lib.FTK_BF16), 0
     _need_cuda(dW_into)
     if dW_into.shape != W.shape or not dW_into.is_contiguous() or dW_into.dtype not in (torch.float32, torch.bfloat16):
         raise _lib.FtkError("dW_into must be a contiguous bf16 or fp32 tensor of the weight's shape")
-    return dW_into, (_lib.FTK_F32 if dW_into.dtype == torch.float32 else _lib.FTK_BF16), 1
+    acc = 1
+    if getattr(dW_into, "_ftk_overwrite", False):
+        dW_into._ftk_overwrite = False
+        acc = 0
+    return dW_into, (_lib.FTK_F32 if dW_into.dtype == torch.float32 else _lib.FTK_BF16), acc
 
 
 def _bwd_impl(H, W, bias, targets, lse, grad_out, n_valid, grad_scale, dw_fp32, dW_into):

@@ -56,3 +56,31 @@ def test_dp_allreduce_c_abi_scales_in_place(cuda_dev):
         torch.cuda.synchronize()
         assert torch.equal(x, want)
     _lib.check(L.ftk_dp_destroy(h), "ftk_dp_destroy")
+
+
+def test_lazy_zero_of_the_fused_loss_gradient(cuda_dev):
+    """GradSync.zero_grad(overwritten_by_fused_loss=W) zeroes everything in W's bucket except W's own gradient and
+    marks that gradient; the next fused loss call overwrites it (no stale content survives), later calls add."""
+    from oracle import oracle as O
+    from kubernetes_cloud_b200 import ops
+    from kubernetes_cloud_b200.dp import GradSync
+    M, d, V = 300, 64, 500
+    g = torch.Generator().manual_seed(4)
+    other = torch.nn.Parameter(torch.randn(37, device="cuda").to(torch.bfloat16))
+    W = torch.nn.Parameter((torch.randn(V, d, generator=g) * 0.05).to(torch.bfloat16).cuda())
+    tail = torch.nn.Parameter(torch.randn(11, device="cuda").to(torch.bfloat16))
+    sync = GradSync([other, W, tail], 0, 1, bucket_bytes=1 << 30, backend="ftk")  # one bucket, fp32 main gradients
+    assert len(sync.buckets) == 1 and sync.main_grads
+    sync.buckets[0].flat.fill_(7.0)  # stale content everywhere
+    sync.zero_grad(overwritten_by_fused_loss=W)
+    assert float(other.main_grad.abs().max()) == 0.0 and float(tail.main_grad.abs().max()) == 0.0
+    assert float(W.main_grad.min()) == 7.0  # not touched by the zeroing pass
+    total = torch.zeros(V, d)
+    for k in range(2):
+        H = torch.randn(M, d, generator=g).to(torch.bfloat16)
+        t = torch.randint(0, V, (M,), generator=g)
+        total += O.lmhead_ce_reference(H, W.detach().cpu(), None, t)["dW"]
+        with sync.no_sync():
+            ops.fused_lmhead_ce(H.cuda().requires_grad_(True), W, None, t.cuda()).backward()
+    assert O.rel_err(W.main_grad, total) < 5e-3  # first call overwrote the 7s, second call added
+    sync.close()

@@ -315,3 +315,22 @@ def test_fp16_request_is_rejected_loudly(tmp_path):
     with pytest.raises(SystemExit) as e:
         finetune.main(["--run-name", "r", "--model", "gpt2", "--dataset", str(ds), "--fp16"])
     assert e.value.code == 1  # runtime failures exit 1 (FT.py:442-444)
+
+
+def test_fused_slab_planner():
+    """ftk_lmhead_ce_fused_plan (host logic, no device): whole 256-row tiles, one slab within the 1 GiB cap, the
+    bench shape split as 6,912 + 9,472 rows (37 row blocks x 8 dH tiles = exactly 4 waves over 74 SM pairs), small
+    batches kept in one slab (short slabs make the dW GEMM epilogue-paced)."""
+    from kubernetes_cloud_b200 import _lib
+    L = _lib.lib()
+    assert L.ftk_lmhead_ce_fused_plan(16384, 2048, 50257, 148, 2) == 9472
+    for M in (1, 300, 2048, 4096):
+        for d in (768, 2048, 4096):
+            assert L.ftk_lmhead_ce_fused_plan(M, d, 50257, 148, 2) == (M + 255) // 256 * 256
+    for M in (8192, 16384, 65536, 262144):
+        for d in (768, 1024, 2048, 4096):
+            for V in (50257, 50400, 32000):
+                r = L.ftk_lmhead_ce_fused_plan(M, d, V, 148, 2)
+                assert r % 256 == 0 and 2816 <= r <= M
+                assert r * ((V + 63) // 64 * 64) * 2 <= 1 << 30
+    assert L.ftk_lmhead_ce_fused_plan(0, 2048, 50257, 148, 2) == 0 and L.ftk_lmhead_ce_fused_plan(4096, 2048, 50257, 148, 3) == 0
