@@ -92,6 +92,8 @@ int ftk_set_option(int32_t key, int32_t value);
 #define FTK_TL_ADAMW 10
 #define FTK_TL_SQNORM 11
 #define FTK_TL_ALLREDUCE 12 /* the NCCL collective, on the communication stream */
+#define FTK_TL_LINEAR_FWD 13
+#define FTK_TL_LINEAR_DX 14
 int ftk_timeline_enable(int32_t on);
 int ftk_timeline_read(int32_t* tags, float* ms, float* start_ms, int32_t max_n);
 
@@ -257,6 +259,27 @@ int ftk_lmhead_ce_fused(const void* H, const void* W, const void* bias, const in
                         int32_t* n_valid, void* dH, void* dW, int32_t dw_dtype, int32_t accumulate, float* dbias,
                         void* dw_done_event, void* workspace, size_t workspace_bytes, int64_t slab_rows, void* stream);
 int ftk_scale_unless_one(void* buf, size_t n, int32_t dtype, const float* factor_dev, int32_t poison, void* stream);
+
+/*
+ * Linear layers of the transformer trunk (the next row after the hot path): the same
+ * TMA -> tcgen05.mma -> TMEM kernel template with a bias / GELU epilogue. Replaces torch.nn.Linear inside HF's
+ * GPT-Neo / GPT-J blocks (the modules finetuner.py trains through model(**inputs), FT.py:479, with gradient
+ * checkpointing on, FT.py:884) and the elementwise passes around their MLP activation.
+ *   ftk_linear_fwd   Y[M,N] = act(X[M,K] . W[N,K]^T + bias[N]), all bf16; act FTK_ACT_GELU_NEW also stores the
+ *                    pre-activation in `pre` (may be NULL) for the backward
+ *   ftk_linear_bwd   dX[M,K] = dY[M,N] . W            (NULL to skip), multiplied elementwise by gelu_new'(dx_mul_pre)
+ *                    when dx_mul_pre (bf16 [M,K], the pre-activation of the GELU layer that produced X) is given:
+ *                    the gradient leaves the GEMM already taken through the activation;
+ *                    dW[N,K] (+)= dY^T . X           (NULL to skip; FTK_BF16 / FTK_F32, accumulate as elsewhere);
+ *                    dbias[N] (+)= column sums of dY  (fp32, NULL to skip)
+ * K and N must be multiples of 64.
+ */
+#define FTK_ACT_NONE 0
+#define FTK_ACT_GELU_NEW 1
+int ftk_linear_fwd(const void* X, const void* W, const void* bias, int64_t M, int32_t K, int32_t N, int32_t act, void* Y,
+                   void* pre, void* stream);
+int ftk_linear_bwd(const void* X, const void* W, const void* dY, const void* dx_mul_pre, int64_t M, int32_t K, int32_t N,
+                   void* dX, void* dW, int32_t dw_dtype, int32_t accumulate, float* dbias, void* stream);
 
 /*
  * Data-parallel gradient all-reduce (replaces DeepSpeed ZeRO's bucketed

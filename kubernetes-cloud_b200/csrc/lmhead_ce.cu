@@ -48,6 +48,8 @@ struct Sched {
   int tiles_per_chunk;  // N tiles per unit
   int n_ntile;          // N tiles in total
   int n_kblk;           // K blocks of BK
+  int k_split;          // >= 1: every (m block, chunk) is cut into k_split units over disjoint K ranges (split-K);
+                        // n_chunks then counts chunk x split pairs and the epilogue is told which split it has
   uint64_t hint_a;      // L2 eviction policy of the A / B operand loads
   uint64_t hint_b;
 };
@@ -60,6 +62,20 @@ __device__ __forceinline__ void decode_unit(const Sched& sc, int u, int& m_blk, 
   const int gm = min(sc.m_group, sc.n_mblk - m_first);  // the last group may be smaller
   chunk = r / gm;
   m_blk = m_first + (r - chunk * gm);
+}
+
+// K range [kb0, kb1) of a unit whose decoded chunk index carries the split (chunk = real chunk * k_split + split).
+__device__ __forceinline__ void split_of(const Sched& sc, int& chunk, int& split, int& kb0, int& kb1) {
+  split = 0;
+  kb0 = 0;
+  kb1 = sc.n_kblk;
+  if (sc.k_split > 1) {
+    split = chunk % sc.k_split;
+    chunk = chunk / sc.k_split;
+    const int per = (sc.n_kblk + sc.k_split - 1) / sc.k_split;
+    kb0 = split * per;
+    kb1 = min(sc.n_kblk, kb0 + per);
+  }
 }
 
 __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
@@ -150,6 +166,7 @@ struct FwdEpi {
       if (st.has) p.ztgt[st.row] = st.zt;
     }
   }
+  static __device__ __forceinline__ void set_split(State&, const Params&, int) {}
   static __device__ __forceinline__ void finish(const EpiCtx&) {}
 };
 
@@ -243,6 +260,7 @@ struct DzEpi {
   }
   template <int BN>
   static __device__ __forceinline__ void end_unit(State&, const Params&) {}
+  static __device__ __forceinline__ void set_split(State&, const Params&, int) {}
   static __device__ __forceinline__ void finish(const EpiCtx& cx) {
     if (cx.lane == 0) tma_store_wait_all<0>();  // all dZ writes complete before the CTA (and its smem) goes away
   }
@@ -373,25 +391,33 @@ struct FwdKeepEpi {
       if (st.has) p.ztgt[st.row] = st.zt;
     }
   }
+  static __device__ __forceinline__ void set_split(State&, const Params&, int) {}
   static __device__ __forceinline__ void finish(const EpiCtx& cx) {
     if (cx.lane == 0) tma_store_wait_all<0>();
   }
 };
 
-// Plain GEMM epilogue: out[row, col] (+)= acc, bf16 or fp32 row-major.
+// Plain GEMM epilogue: out[row, col] (+)= acc, bf16 or fp32 row-major.  Under split-K each split writes its partial
+// sums to its own copy of the output, split_stride elements apart (summed afterwards in a fixed order).
 template <bool kF32>
 struct StoreEpi {
   static constexpr uint32_t kSmemBytes = 0;
   struct Params {
     void* out;
     int rows, cols, ld, accumulate;
+    size_t split_stride;
   };
   struct State {
     int row;
+    size_t base;  // element offset of this unit's split
   };
   template <int BN>
   static __device__ __forceinline__ void begin_unit(State& st, const Params&, int row, int) {
     st.row = row;
+    st.base = 0;
+  }
+  static __device__ __forceinline__ void set_split(State& st, const Params& p, int split) {
+    st.base = static_cast<size_t>(split) * p.split_stride;
   }
   template <int BN>
   static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0, const EpiCtx&) {
@@ -405,7 +431,7 @@ struct StoreEpi {
       if (st.row >= p.rows) {
         // rows past the end: nothing to store (no `continue`: the next tcgen05.ld needs a converged warp)
       } else if constexpr (kF32) {
-        float4* dst = reinterpret_cast<float4*>(static_cast<float*>(p.out) + static_cast<size_t>(st.row) * p.ld + col0);
+        float4* dst = reinterpret_cast<float4*>(static_cast<float*>(p.out) + st.base + static_cast<size_t>(st.row) * p.ld + col0);
 #pragma unroll
         for (int q = 0; q < 8; ++q) {
           if (col0 + q * 4 >= p.cols) break;
@@ -420,8 +446,8 @@ struct StoreEpi {
           dst[q] = o;
         }
       } else {
-        uint4* dst = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + static_cast<size_t>(st.row) * p.ld +
-                                              col0);
+        uint4* dst = reinterpret_cast<uint4*>(static_cast<__nv_bfloat16*>(p.out) + st.base +
+                                              static_cast<size_t>(st.row) * p.ld + col0);
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
           if (col0 + q * 8 >= p.cols) break;
@@ -438,6 +464,96 @@ struct StoreEpi {
           }
           dst[q] = make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]), pack_bf16x2(x[4], x[5]),
                               pack_bf16x2(x[6], x[7]));
+        }
+      }
+    }
+  }
+  template <int BN>
+  static __device__ __forceinline__ void end_unit(State&, const Params&) {}
+  static __device__ __forceinline__ void finish(const EpiCtx&) {}
+};
+
+// Linear-layer epilogue (the trunk's projections): bf16 out[row, col] = f(acc + bias[col]).
+//   act == 1: f = gelu_new (the tanh form HF's GPT-Neo / GPT-J MLPs use); `pre` (optional) also receives acc + bias,
+//             the value the backward needs;
+//   mul_pre != null: out = acc * gelu_new'(mul_pre[row, col]) -- the dX GEMM of the layer AFTER a GELU hands back the
+//             gradient with respect to the pre-activation directly, so no elementwise pass ever touches [M, 4d].
+struct LinearEpi {
+  static constexpr uint32_t kSmemBytes = 0;
+  struct Params {
+    __nv_bfloat16* out;
+    __nv_bfloat16* pre;
+    const __nv_bfloat16* bias;
+    const __nv_bfloat16* mul_pre;
+    int rows, cols, ld, act;
+  };
+  struct State {
+    int row;
+  };
+  static __device__ __forceinline__ float tanh_fast(float x) {
+    float r;
+    asm("tanh.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+  }
+  static __device__ __forceinline__ float gelu_new(float x) {
+    const float u = 0.7978845608028654f * fmaf(0.044715f * x, x * x, x);
+    return 0.5f * x * (1.f + tanh_fast(u));
+  }
+  static __device__ __forceinline__ float gelu_new_grad(float x) {
+    const float x2 = x * x;
+    const float t = tanh_fast(0.7978845608028654f * fmaf(0.044715f * x, x2, x));
+    const float du = 0.7978845608028654f * fmaf(3.f * 0.044715f, x2, 1.f);
+    return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * du;
+  }
+  template <int BN>
+  static __device__ __forceinline__ void begin_unit(State& st, const Params&, int row, int) {
+    st.row = row;
+  }
+  static __device__ __forceinline__ void set_split(State&, const Params&, int) {}
+  template <int BN>
+  static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0, const EpiCtx&) {
+#pragma unroll 1
+    for (int c = 0; c < BN / 32; ++c) {
+      const int col0 = n0 + c * 32;
+      if (col0 >= p.cols) break;  // warp-uniform
+      float v[32];
+      tmem_ld32(taddr + c * 32, v);
+      tmem_ld_wait();
+      if (st.row < p.rows) {  // no `continue`: the next tcgen05.ld needs a converged warp
+        const size_t off = static_cast<size_t>(st.row) * p.ld + col0;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          if (col0 + q * 8 >= p.cols) break;  // cols is a multiple of 8
+          float* x = v + 8 * q;
+          if (p.bias != nullptr) {
+            const uint4 bw = __ldg(reinterpret_cast<const uint4*>(p.bias + col0) + q);
+            const uint32_t b4[4] = {bw.x, bw.y, bw.z, bw.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&b4[e]);
+              x[2 * e] += __low2float(h);
+              x[2 * e + 1] += __high2float(h);
+            }
+          }
+          if (p.mul_pre != nullptr) {
+            const uint4 pw = *(reinterpret_cast<const uint4*>(p.mul_pre + off) + q);
+            const uint32_t p4[4] = {pw.x, pw.y, pw.z, pw.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&p4[e]);
+              x[2 * e] *= gelu_new_grad(__low2float(h));
+              x[2 * e + 1] *= gelu_new_grad(__high2float(h));
+            }
+          }
+          if (p.act == 1) {
+            if (p.pre != nullptr)
+              *(reinterpret_cast<uint4*>(p.pre + off) + q) = make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]),
+                                                                        pack_bf16x2(x[4], x[5]), pack_bf16x2(x[6], x[7]));
+#pragma unroll
+            for (int e = 0; e < 8; ++e) x[e] = gelu_new(x[e]);
+          }
+          *(reinterpret_cast<uint4*>(p.out + off) + q) = make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]),
+                                                                    pack_bf16x2(x[4], x[5]), pack_bf16x2(x[6], x[7]));
         }
       }
     }
@@ -518,14 +634,15 @@ __global__ void __launch_bounds__(kThreads, 1)
       int stage = 0;
       uint32_t phase = 0;
       for (int u = cl; u < sc.n_units; u += n_cl) {
-        int m_blk, chunk;
+        int m_blk, chunk, split, kb0, kb1;
         decode_unit(sc, u, m_blk, chunk);
+        split_of(sc, chunk, split, kb0, kb1);
         const int m0 = (m_blk * kCG + static_cast<int>(rank)) * BM;
         const int nt_begin = chunk * sc.tiles_per_chunk;
         const int nt_end = min(nt_begin + sc.tiles_per_chunk, sc.n_ntile);
         for (int nt = nt_begin; nt < nt_end; ++nt) {
           const int n0 = nt * BN + static_cast<int>(rank) * LOAD_BN;
-          for (int kb = 0; kb < sc.n_kblk; ++kb) {
+          for (int kb = kb0; kb < kb1; ++kb) {
             mbar_wait(&empty[stage], phase ^ 1);
             uint64_t* bar = &full[stage];
             if constexpr (kCG == 1) {
@@ -589,8 +706,9 @@ __global__ void __launch_bounds__(kThreads, 1)
       uint32_t phase = 0;
       uint32_t it = 0;
       for (int u = cl; u < sc.n_units; u += n_cl) {
-        int m_blk, chunk;
+        int m_blk, chunk, split, kb0, kb1;
         decode_unit(sc, u, m_blk, chunk);
+        split_of(sc, chunk, split, kb0, kb1);
         const int nt_begin = chunk * sc.tiles_per_chunk;
         const int nt_end = min(nt_begin + sc.tiles_per_chunk, sc.n_ntile);
         for (int nt = nt_begin; nt < nt_end; ++nt, ++it) {
@@ -598,7 +716,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           mbar_wait(&tempty[as], aphase ^ 1);
           tc_fence_after();
           const uint32_t tmem_d = tmem_base + as * BN;
-          for (int kb = 0; kb < sc.n_kblk; ++kb) {
+          for (int kb = kb0; kb < kb1; ++kb) {
             mbar_wait(&full[stage], phase);
             tc_fence_after();
             const uint32_t a_addr = smem_u32(sA + stage * L::A_BYTES);
@@ -607,10 +725,10 @@ __global__ void __launch_bounds__(kThreads, 1)
             for (int k = 0; k < BK / UK; ++k) {
               const uint64_t adesc = make_sw128_desc(a_addr + k * a_kstep, kAMN ? kLboMN : 0u, kSbo);
               const uint64_t bdesc = make_sw128_desc(b_addr + k * b_kstep, kBMN ? kLboMN : 0u, kSbo);
-              umma_bf16<kCG>(tmem_d, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+              umma_bf16<kCG>(tmem_d, adesc, bdesc, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
             }
             umma_commit<kCG>(&empty[stage]);  // frees the smem stage once these MMAs have read it
-            if (kb == sc.n_kblk - 1) umma_commit<kCG>(&tfull[as]);
+            if (kb == kb1 - 1) umma_commit<kCG>(&tfull[as]);
             if (++stage == kStages) {
               stage = 0;
               phase ^= 1;
@@ -627,10 +745,12 @@ __global__ void __launch_bounds__(kThreads, 1)
     typename Epi::State st = {};
     uint32_t it = 0;
     for (int u = cl; u < sc.n_units; u += n_cl) {
-      int m_blk, chunk;
+      int m_blk, chunk, split, kb0, kb1;
       decode_unit(sc, u, m_blk, chunk);
+      split_of(sc, chunk, split, kb0, kb1);
       const int row = (m_blk * kCG + static_cast<int>(rank)) * BM + row_in_tile;
       Epi::template begin_unit<BN>(st, ep, row, chunk);
+      Epi::set_split(st, ep, split);
       const int nt_begin = chunk * sc.tiles_per_chunk;
       const int nt_end = min(nt_begin + sc.tiles_per_chunk, sc.n_ntile);
       for (int nt = nt_begin; nt < nt_end; ++nt, ++it) {
@@ -774,6 +894,25 @@ __global__ void __launch_bounds__(256) scale_unless_one_kernel(T* __restrict__ b
       }
     }
     b[i] = v;
+  }
+}
+
+// dH = sum over the split-K copies, in split order (fixed, so the result does not depend on scheduling), as bf16.
+// rows * d is a multiple of 8 (d is a multiple of 64).
+__global__ void __launch_bounds__(256) dh_reduce_kernel(const float* __restrict__ partials, int k_split, size_t stride,
+                                                        size_t n_vec, __nv_bfloat16* __restrict__ out) {
+  for (size_t i = blockIdx.x * static_cast<size_t>(256) + threadIdx.x; i < n_vec; i += gridDim.x * static_cast<size_t>(256)) {
+    float acc[8];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+    for (int sp = 0; sp < k_split; ++sp) {
+      const float4* src = reinterpret_cast<const float4*>(partials + static_cast<size_t>(sp) * stride) + 2 * i;
+      const float4 a = __ldcs(src), b = __ldcs(src + 1);
+      acc[0] += a.x, acc[1] += a.y, acc[2] += a.z, acc[3] += a.w;
+      acc[4] += b.x, acc[5] += b.y, acc[6] += b.z, acc[7] += b.w;
+    }
+    reinterpret_cast<uint4*>(out)[i] = make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]),
+                                                  pack_bf16x2(acc[4], acc[5]), pack_bf16x2(acc[6], acc[7]));
   }
 }
 
@@ -1015,6 +1154,7 @@ int run_fwd(const void* H, const void* W, const void* bias, const int64_t* targe
   if (int rc = make_tmap(&tmA, H, d, M, static_cast<uint64_t>(d) * 2, BK, BM)) return rc;
   if (int rc = make_tmap(&tmB, W, d, V, static_cast<uint64_t>(d) * 2, BK, BN / kCG)) return rc;
   Sched sc;
+  sc.k_split = 1;
   const int n_mblk = ceil_div(M, BM * kCG);
   sc.n_ntile = ceil_div(V, BN);
   int n_chunks;
@@ -1059,6 +1199,7 @@ int run_fwd_keep(const void* H, const void* W, const void* bias, const int64_t* 
   if (int rc = make_tmap(&tmA, H, d, M, static_cast<uint64_t>(d) * 2, BK, BM)) return rc;
   if (int rc = make_tmap(&tmB, W, d, V, static_cast<uint64_t>(d) * 2, BK, BN / kCG)) return rc;
   Sched sc;
+  sc.k_split = 1;
   const int n_mblk = ceil_div(M, BM * kCG);
   sc.n_ntile = ceil_div(V, BN);
   int n_chunks;
@@ -1105,6 +1246,8 @@ struct GradGemmPlan {
   bool overlap_tail = false;
   bool full_sms = false;  // ignore the SM reserve for both GEMMs (slabs whose gradients nobody is waiting for yet)
   cudaEvent_t dw_done = nullptr;
+  float* dh_partials = nullptr;  // scratch for a split-K dH GEMM (plan_dh_split), or null: never split
+  size_t dh_partial_bytes = 0;
 };
 
 template <int kCG>
@@ -1128,6 +1271,7 @@ int run_bwd_slab(const void* H, const void* W, const void* bias, const int64_t* 
     if (int rc = make_tmap(&tmA, H, d, rows, static_cast<uint64_t>(d) * 2, BK, BM)) return rc;
     if (int rc = make_tmap(&tmB, W, d, V, static_cast<uint64_t>(d) * 2, BK, BN / kCG)) return rc;
     Sched sc;
+    sc.k_split = 1;
     const int n_mblk = ceil_div(rows, BM * kCG);
     sc.n_ntile = ceil_div(V, BN);
     int n_chunks;
@@ -1155,32 +1299,82 @@ int run_bwd_slab(const void* H, const void* W, const void* bias, const int64_t* 
   return run_grad_gemms<kCG>(H, W, rows, d, V, dH, dW, dw_dtype, accumulate, dbias, dz, sm_count, st, GradGemmPlan());
 }
 
+// Split-K plan of the dH GEMM.  Its units are (row block x N tile) with the whole vocabulary as K: at d = 768 a slab
+// of 10,496 rows is 41 x 3 = 123 units, 1.66 waves over 74 SM pairs charged as 2.  Cutting every unit into k_split
+// pieces over disjoint vocabulary ranges fills the last wave (123 x 3 = 369 = 4.99 waves of a third the length); each
+// piece writes fp32 partial sums to its own copy of the output and dh_reduce_kernel adds the copies in a fixed order
+// (deterministic, no atomics).  Used when it cuts the charged time by more than 8 % and the copies stay small.
+constexpr size_t kDhPartialBudget = size_t(160) << 20;
+inline int plan_dh_split(int64_t rows, int d, int V, int n_groups, int kCG) {
+  const int64_t units = static_cast<int64_t>(ceil_div(rows, BM * kCG)) * ceil_div(d, 256);
+  const int n_kblk = ceil_div(V, BK);
+  int best = 1;
+  double best_t = static_cast<double>(ceil_div(units, n_groups)) * n_kblk;
+  for (int ks = 2; ks <= 8; ++ks) {
+    if (n_kblk < 16 * ks) break;  // every split must own K blocks
+    if (static_cast<size_t>(ks) * round_up(rows, BM * kCG) * round_up(d, 256) * 4 > kDhPartialBudget) break;
+    // each piece pays its own pipeline fill and an fp32 epilogue: ~24 K blocks' worth
+    const double t = static_cast<double>(ceil_div(units * ks, n_groups)) * (static_cast<double>(ceil_div(n_kblk, ks)) + 24);
+    if (t < best_t * 0.92 && t < static_cast<double>(ceil_div(units, n_groups)) * n_kblk * 0.92) {
+      best_t = t;
+      best = ks;
+    }
+  }
+  return best;
+}
+inline size_t dh_partial_bytes(int64_t rows, int d, int V, int n_groups, int kCG) {
+  const int ks = plan_dh_split(rows, d, V, n_groups, kCG);
+  return ks > 1 ? static_cast<size_t>(ks) * round_up(rows, BM * kCG) * d * 4 : 0;
+}
+
 // dH[rows, d] = dZ[rows, V] . W[V, d]: A K-major (K = V, the tail zero-filled by TMA), B MN-major.
+// partials != null and k_split > 1: split-K into fp32 copies (see plan_dh_split), reduced into dH afterwards.
 template <int kCG, int BN>
 int run_dh(const void* W, int64_t rows, int d, int V, void* dH, __nv_bfloat16* dz, int sm_count, cudaStream_t st,
-           int reserve) {
+           int reserve, float* partials = nullptr, int k_split = 1) {
   constexpr int kStages = (BN == 256) ? ((kCG == 1) ? 4 : 6) : ((kCG == 1) ? 6 : 8);
   const int64_t ld = dz_pitch(V);
   CUtensorMap tmA, tmB;
   if (int rc = make_tmap(&tmA, dz, V, rows, static_cast<uint64_t>(ld) * 2, BK, BM)) return rc;
   if (int rc = make_tmap(&tmB, W, d, V, static_cast<uint64_t>(d) * 2, 64, BK)) return rc;
+  if (partials == nullptr) k_split = 1;
   Sched sc;
   const int n_mblk = ceil_div(rows, BM * kCG);
   sc.n_ntile = ceil_div(d, BN);
   sc.tiles_per_chunk = 1;
-  sc.n_units = n_mblk * sc.n_ntile;
+  sc.k_split = k_split;
+  sc.n_chunks = sc.n_ntile * k_split;  // (N tile, split) pairs
+  sc.n_units = n_mblk * sc.n_chunks;
   sc.n_mblk = n_mblk;
-  sc.n_chunks = sc.n_ntile;
-  sc.m_group = 1;  // N tiles of one m block are adjacent: the dZ rows are read from HBM once
+  sc.m_group = 1;  // all pieces of one m block are adjacent: its dZ rows stream from HBM once
   sc.n_kblk = ceil_div(V, BK);
   pick_hints("nnn", 2, &sc.hint_a, &sc.hint_b, nullptr);
+  ftk::TimelineScope tl_(FTK_TL_DH, st);
+  if (k_split > 1) {
+    StoreEpi<true>::Params ep;
+    ep.out = partials;
+    ep.rows = static_cast<int>(rows);
+    ep.cols = d;
+    ep.ld = d;
+    ep.accumulate = 0;
+    ep.split_stride = static_cast<size_t>(round_up(rows, BM * kCG)) * d;
+    if (int rc = launch_umma<kCG, BN, kStages, false, true, StoreEpi<true>>(tmA, tmB, sc, ep, sm_count, st, reserve))
+      return rc;
+    const size_t n_vec = static_cast<size_t>(rows) * d / 8;
+    size_t blocks = (n_vec + 255) / 256;
+    if (blocks > static_cast<size_t>(sm_count) * 8) blocks = static_cast<size_t>(sm_count) * 8;
+    dh_reduce_kernel<<<static_cast<unsigned>(blocks), 256, 0, st>>>(partials, k_split, ep.split_stride, n_vec,
+                                                                  static_cast<__nv_bfloat16*>(dH));
+    FTK_CUDA_CHECK(cudaGetLastError());
+    return FTK_OK;
+  }
   StoreEpi<false>::Params ep;
   ep.out = dH;
   ep.rows = static_cast<int>(rows);
   ep.cols = d;
   ep.ld = d;
   ep.accumulate = 0;
-  ftk::TimelineScope tl_(FTK_TL_DH, st);
+  ep.split_stride = 0;
   return launch_umma<kCG, BN, kStages, false, true, StoreEpi<false>>(tmA, tmB, sc, ep, sm_count, st, reserve);
 }
 
@@ -1195,6 +1389,7 @@ int run_dw(const void* H, int64_t rows, int d, int V, void* dW, int dw_dtype, in
   if (int rc = make_tmap(&tmA, dz, V, rows, static_cast<uint64_t>(ld) * 2, 64, BK)) return rc;
   if (int rc = make_tmap(&tmB, H, d, rows, static_cast<uint64_t>(d) * 2, 64, BK)) return rc;
   Sched sc;
+  sc.k_split = 1;
   const int n_mblk = ceil_div(V, BM * kCG);
   sc.n_ntile = ceil_div(d, BN);
   sc.tiles_per_chunk = 1;
@@ -1212,6 +1407,7 @@ int run_dw(const void* H, int64_t rows, int d, int V, void* dW, int dw_dtype, in
     ep.cols = d;
     ep.ld = d;
     ep.accumulate = accumulate;
+  ep.split_stride = 0;
     return launch_umma<kCG, BN, kStages, true, true, StoreEpi<true>>(tmA, tmB, sc, ep, sm_count, st, reserve);
   }
   StoreEpi<false>::Params ep;
@@ -1220,6 +1416,7 @@ int run_dw(const void* H, int64_t rows, int d, int V, void* dW, int dw_dtype, in
   ep.cols = d;
   ep.ld = d;
   ep.accumulate = accumulate;
+  ep.split_stride = 0;
   return launch_umma<kCG, BN, kStages, true, true, StoreEpi<false>>(tmA, tmB, sc, ep, sm_count, st, reserve);
 }
 
@@ -1252,7 +1449,12 @@ int run_grad_gemms(const void* H, const void* W, int64_t rows, int d, int V, voi
   if (dh_bn == 128) {
     if (int rc = run_dh<kCG, 128>(W, rows, d, V, dH, dz, sm_count, st, res_dh)) return rc;
   } else {
-    if (int rc = run_dh<kCG, 256>(W, rows, d, V, dH, dz, sm_count, st, res_dh)) return rc;
+    int ks = 1;
+    if (plan.dh_partials != nullptr) {
+      ks = plan_dh_split(rows, d, V, n_groups, kCG);
+      if (static_cast<size_t>(ks) * round_up(rows, BM * kCG) * d * 4 > plan.dh_partial_bytes) ks = 1;
+    }
+    if (int rc = run_dh<kCG, 256>(W, rows, d, V, dH, dz, sm_count, st, res_dh, plan.dh_partials, ks)) return rc;
   }
   if (!plan.overlap_tail)
     if (int rc = run_dw<kCG>(H, rows, d, V, dW, dw_dtype, accumulate, dz, sm_count, st, res_dw)) return rc;
@@ -1433,10 +1635,12 @@ int64_t slab_cost(int64_t r, int d, int V, int n_groups, int kCG) {
   int n_chunks, tpc;
   plan_chunks(n_mblk, ceil_div(V, 256), n_groups, &n_chunks, &tpc);
   int64_t cost = static_cast<int64_t>(ceil_div(static_cast<int64_t>(n_mblk) * n_chunks, n_groups)) * tpc * (d / 64);
-  const int64_t w256 = ceil_div(static_cast<int64_t>(n_mblk) * ceil_div(d, 256), n_groups) * 2;
-  const int64_t w128 = ceil_div(static_cast<int64_t>(n_mblk) * ceil_div(d, 128), n_groups);
-  const int64_t w = (w128 * kNarrowTilePenaltyPct < w256 * 100) ? (w128 * kNarrowTilePenaltyPct + 99) / 100 : w256;
-  cost += w * ceil_div(V, 64) / 2;
+  {  // dH: whole waves of (row block x N tile) units, split over K when that fills the last wave (plan_dh_split)
+    const int64_t units = static_cast<int64_t>(n_mblk) * ceil_div(d, 256);
+    const int ks = plan_dh_split(r, d, V, n_groups, kCG);
+    const int64_t n_kblk = ceil_div(V, 64);
+    cost += ceil_div(units * ks, n_groups) * (ceil_div(n_kblk, ks) + (ks > 1 ? 24 : 0));
+  }
   // dW: K = the slab's rows.  The work is the same whatever the split, but a 256 x 256 output tile's epilogue
   // (TMEM read, read-modify-write of dW) takes about as long as 48 K blocks of MMAs, so slabs under ~3,000 rows make
   // the dW GEMM epilogue-paced (measured: 4,096 rows as 2 x 2,048 is 30 % slower than as one slab).
@@ -1482,6 +1686,8 @@ struct FusedWorkspace {
   void* fwd;
   float* cref[2];
   __nv_bfloat16* probs[2];
+  float* dh_partials;
+  size_t dh_partial_bytes;
   int64_t slab;
   int n_buf;
   size_t fwd_bytes, bytes;
@@ -1490,7 +1696,7 @@ struct FusedWorkspace {
 // One set of forward statistics (a slab's finalize has run before the next sweep starts), and a numerators slab plus
 // its reference-maxima table per buffer: two buffers when the rows make two or more slabs, so that the conversion of
 // one slab can run on the side stream while the next slab's sweep fills the other.
-FusedWorkspace carve_fused(void* base, int64_t M, int V, int64_t slab) {
+FusedWorkspace carve_fused(void* base, int64_t M, int d, int V, int64_t slab, int sm_count, int kCG) {
   FusedWorkspace w;
   if (slab > M) slab = M;
   w.slab = slab;
@@ -1511,6 +1717,15 @@ FusedWorkspace carve_fused(void* base, int64_t M, int V, int64_t slab) {
     w.probs[b] = reinterpret_cast<__nv_bfloat16*>(p + off);
     off += static_cast<size_t>(round_up(slab, 256)) * dz_pitch(V) * 2;
   }
+  // split-K scratch of the dH GEMM: the larger need of the two slab sizes in use (full slab, remainder)
+  const int n_groups = (sm_count > kCG ? sm_count : kCG) / kCG;
+  w.dh_partial_bytes = dh_partial_bytes(slab, d, V, n_groups, kCG);
+  if (M % slab != 0) {
+    const size_t r = dh_partial_bytes(M % slab, d, V, n_groups, kCG);
+    if (r > w.dh_partial_bytes) w.dh_partial_bytes = r;
+  }
+  w.dh_partials = w.dh_partial_bytes != 0 ? reinterpret_cast<float*>(p + off) : nullptr;
+  off += round_up(w.dh_partial_bytes, 256);
   w.bytes = off;
   return w;
 }
@@ -1553,7 +1768,10 @@ extern "C" int64_t ftk_lmhead_ce_fused_plan(int64_t M, int32_t d, int32_t V, int
 extern "C" size_t ftk_lmhead_ce_fused_workspace(int64_t M, int32_t d, int32_t V, int64_t slab_rows) {
   const int64_t slab = ftk_lmhead_ce_fused_slab_rows(M, d, V, slab_rows);
   if (slab <= 0) return 0;
-  return carve_fused(nullptr, M, V, slab).bytes;
+  ftk::DeviceInfo di;
+  if (ftk::get_device_info(&di)) return 0;
+  // the base only matters for the pointers, not for the size
+  return carve_fused(reinterpret_cast<void*>(uintptr_t(256)), M, d, V, slab, di.sm_count, cta_group()).bytes;
 }
 
 extern "C" int ftk_lmhead_ce_fused(const void* H, const void* W, const void* bias, const int64_t* targets, int64_t M,
@@ -1571,7 +1789,7 @@ extern "C" int ftk_lmhead_ce_fused(const void* H, const void* W, const void* bia
               "ftk_lmhead_ce_fused: dH/dW must be 16-byte aligned");
   int64_t slab = 0;
   if (int rc = fused_slab_rows(M, d, V, slab_rows, &slab)) return rc;
-  const FusedWorkspace fw = carve_fused(workspace, M, V, slab);
+  const FusedWorkspace fw = carve_fused(workspace, M, d, V, slab, di.sm_count, cta_group());
   if (workspace_bytes < fw.bytes)
     return ftk::fail(FTK_EWORKSPACE, "ftk_lmhead_ce_fused: workspace %zu bytes < required %zu", workspace_bytes,
                      fw.bytes);
@@ -1668,6 +1886,8 @@ extern "C" int ftk_lmhead_ce_fused(const void* H, const void* W, const void* bia
     plan.overlap_tail = (i == n_slabs - 1) && dw_done_event != nullptr;
     plan.full_sms = !plan.overlap_tail;  // the SM reserve only matters where a collective can run beside us
     plan.dw_done = static_cast<cudaEvent_t>(dw_done_event);
+    plan.dh_partials = fw.dh_partials;
+    plan.dh_partial_bytes = fw.dh_partial_bytes;
     return pair ? run_grad_gemms<2>(Hs, W, sl.rows, d, V, dHs, dW, dw_dtype, acc, dbias, fw.probs[b], di.sm_count, st,
                                     plan)
                 : run_grad_gemms<1>(Hs, W, sl.rows, d, V, dHs, dW, dw_dtype, acc, dbias, fw.probs[b], di.sm_count, st,
@@ -1704,6 +1924,121 @@ extern "C" int ftk_scale_unless_one(void* buf, size_t n, int32_t dtype, const fl
     scale_unless_one_kernel<__nv_bfloat16><<<static_cast<unsigned>(blocks), 256, 0, st>>>(
         static_cast<__nv_bfloat16*>(buf), n_vec, factor_dev, poison);
   FTK_CUDA_CHECK(cudaGetLastError());
+  return FTK_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Linear layers of the transformer trunk on the same kernel template (include/ftk.h: ftk_linear_fwd / ftk_linear_bwd).
+namespace {
+
+int check_linear(const void* X, const void* W, int64_t M, int K, int N, ftk::DeviceInfo* di) {
+  FTK_REQUIRE(X && W, "ftk_linear: null X or W");
+  FTK_REQUIRE(M > 0 && M < (int64_t(1) << 30), "ftk_linear: M=%lld out of range", static_cast<long long>(M));
+  FTK_REQUIRE(K > 0 && K % 64 == 0 && N > 0 && N % 64 == 0, "ftk_linear: K=%d and N=%d must be positive multiples of 64",
+              K, N);
+  if (int rc = ftk::get_device_info(di)) return rc;
+  if (di->cc_major != 10)
+    return ftk::fail(FTK_EUNSUPPORTED, "ftk_linear needs an sm_100 device (tcgen05/TMEM); found sm_%d%d", di->cc_major,
+                     di->cc_minor);
+  return FTK_OK;
+}
+
+// out[M, N] = f(A[M, Kd] . B^T), A K-major; B K-major ([N, Kd] rows) or MN-major ([Kd, N] rows).
+template <int kCG, bool kBMN>
+int run_linear_gemm(const void* A, const void* B, int64_t M, int Kd, int N, const LinearEpi::Params& ep_in, int sm_count,
+                    cudaStream_t st, int tl_tag) {
+  constexpr int BN = 256;
+  constexpr int kStages = (kCG == 1) ? 4 : 6;
+  CUtensorMap tmA, tmB;
+  if (int rc = make_tmap(&tmA, A, Kd, M, static_cast<uint64_t>(Kd) * 2, BK, BM)) return rc;
+  if constexpr (kBMN) {
+    if (int rc = make_tmap(&tmB, B, N, Kd, static_cast<uint64_t>(N) * 2, 64, BK)) return rc;
+  } else {
+    if (int rc = make_tmap(&tmB, B, Kd, N, static_cast<uint64_t>(Kd) * 2, BK, BN / kCG)) return rc;
+  }
+  Sched sc;
+  sc.k_split = 1;
+  const int n_mblk = ceil_div(M, BM * kCG);
+  sc.n_ntile = ceil_div(N, BN);
+  const int usable = sm_count - sm_reserve();
+  int n_chunks;
+  plan_chunks(n_mblk, sc.n_ntile, (usable > kCG ? usable : kCG) / kCG, &n_chunks, &sc.tiles_per_chunk);
+  sc.n_units = n_mblk * n_chunks;
+  sc.n_mblk = n_mblk;
+  sc.n_chunks = n_chunks;
+  sc.m_group = pick_m_group(n_mblk, BM * kCG, Kd);
+  sc.n_kblk = ceil_div(Kd, BK);
+  pick_hints("nnn", 0, &sc.hint_a, &sc.hint_b, nullptr);
+  ftk::TimelineScope tl_(tl_tag, st);
+  return launch_umma<kCG, BN, kStages, false, kBMN, LinearEpi>(tmA, tmB, sc, ep_in, sm_count, st);
+}
+
+}  // namespace
+
+extern "C" int ftk_linear_fwd(const void* X, const void* W, const void* bias, int64_t M, int32_t K, int32_t N,
+                              int32_t act, void* Y, void* pre, void* stream) {
+  ftk::DeviceInfo di;
+  if (int rc = check_linear(X, W, M, K, N, &di)) return rc;
+  FTK_REQUIRE(Y != nullptr, "ftk_linear_fwd: null output");
+  FTK_REQUIRE(act == FTK_ACT_NONE || act == FTK_ACT_GELU_NEW, "ftk_linear_fwd: bad activation code %d", act);
+  FTK_REQUIRE(((reinterpret_cast<uintptr_t>(Y) | reinterpret_cast<uintptr_t>(pre) | reinterpret_cast<uintptr_t>(bias)) & 15) == 0,
+              "ftk_linear_fwd: Y / pre / bias must be 16-byte aligned");
+  LinearEpi::Params ep;
+  ep.out = static_cast<__nv_bfloat16*>(Y);
+  ep.pre = static_cast<__nv_bfloat16*>(pre);
+  ep.bias = static_cast<const __nv_bfloat16*>(bias);
+  ep.mul_pre = nullptr;
+  ep.rows = static_cast<int>(M);
+  ep.cols = N;
+  ep.ld = N;
+  ep.act = act;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (cta_group() == 2 && di.sm_count >= 2)
+    return run_linear_gemm<2, false>(X, W, M, K, N, ep, di.sm_count, st, FTK_TL_LINEAR_FWD);
+  return run_linear_gemm<1, false>(X, W, M, K, N, ep, di.sm_count, st, FTK_TL_LINEAR_FWD);
+}
+
+extern "C" int ftk_linear_bwd(const void* X, const void* W, const void* dY, const void* dx_mul_pre, int64_t M,
+                              int32_t K, int32_t N, void* dX, void* dW, int32_t dw_dtype, int32_t accumulate,
+                              float* dbias, void* stream) {
+  ftk::DeviceInfo di;
+  if (int rc = check_linear(X, W, M, K, N, &di)) return rc;
+  FTK_REQUIRE(dY != nullptr, "ftk_linear_bwd: null dY");
+  FTK_REQUIRE(dw_dtype == FTK_BF16 || dw_dtype == FTK_F32, "ftk_linear_bwd: bad dw_dtype %d", dw_dtype);
+  FTK_REQUIRE(((reinterpret_cast<uintptr_t>(dX) | reinterpret_cast<uintptr_t>(dW) | reinterpret_cast<uintptr_t>(dx_mul_pre)) & 15) == 0,
+              "ftk_linear_bwd: dX / dW / dx_mul_pre must be 16-byte aligned");
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const bool pair = cta_group() == 2 && di.sm_count >= 2;
+  if (dX != nullptr) {  // dX[M, K] = dY[M, N] . W[N, K]  (times gelu_new'(dx_mul_pre) when given)
+    LinearEpi::Params ep;
+    ep.out = static_cast<__nv_bfloat16*>(dX);
+    ep.pre = nullptr;
+    ep.bias = nullptr;
+    ep.mul_pre = static_cast<const __nv_bfloat16*>(dx_mul_pre);
+    ep.rows = static_cast<int>(M);
+    ep.cols = K;
+    ep.ld = K;
+    ep.act = FTK_ACT_NONE;
+    const int rc = pair ? run_linear_gemm<2, true>(dY, W, M, N, K, ep, di.sm_count, st, FTK_TL_LINEAR_DX)
+                        : run_linear_gemm<1, true>(dY, W, M, N, K, ep, di.sm_count, st, FTK_TL_LINEAR_DX);
+    if (rc) return rc;
+  }
+  if (dW != nullptr) {  // dW[N, K] (+)= dY^T[N, M] . X[M, K]: the lm_head's dW GEMM with V = N, d = K
+    __nv_bfloat16* dy = const_cast<__nv_bfloat16*>(static_cast<const __nv_bfloat16*>(dY));
+    // run_dw reads its A operand through a [rows][round_up(V, 64)] pitch: N is a multiple of 64, so the pitch is N
+    const int rc = pair ? run_dw<2>(X, M, K, N, dW, dw_dtype, accumulate, dy, di.sm_count, st, -1)
+                        : run_dw<1>(X, M, K, N, dW, dw_dtype, accumulate, dy, di.sm_count, st, -1);
+    if (rc) return rc;
+  }
+  if (dbias != nullptr) {  // dbias[N] (+)= column sums of dY
+    if (!accumulate) FTK_CUDA_CHECK(cudaMemsetAsync(dbias, 0, sizeof(float) * N, st));
+    ftk::TimelineScope tl_(FTK_TL_DBIAS, st);
+    const int rows_per_block = 256;
+    dim3 grid(ceil_div(N, 256), ceil_div(M, rows_per_block));
+    dbias_kernel<<<grid, 128, 0, st>>>(static_cast<const __nv_bfloat16*>(dY), static_cast<int>(M), N, N, rows_per_block,
+                                       dbias);
+    FTK_CUDA_CHECK(cudaGetLastError());
+  }
   return FTK_OK;
 }
 

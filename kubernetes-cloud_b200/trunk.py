@@ -1,0 +1,212 @@
+"""Linear layers and MLP of the transformer trunk on the B200 kernels (first pieces).
+
+The reference trains whatever HF causal LM ``--model`` names through ``model(**inputs)`` (FT.py:479) with gradient
+checkpointing on (FT.py:884).  The trunk is third-party code; this module swaps the pieces of it that the existing
+tcgen05 kernel template covers, leaving the module tree, parameter names and checkpoints untouched:
+
+  ``linear(x, weight, bias)``                  torch.nn.functional.linear            -> ftk_linear_fwd / ftk_linear_bwd
+  ``mlp_gelu_new(x, w_fc, b_fc, w_proj, b_proj)``   c_proj(gelu_new(c_fc(x)))       -> two GEMMs; bias + GELU live in the first
+                                                one's epilogue, and the GELU's derivative in the epilogue of the second
+                                                one's dX GEMM, so no elementwise kernel ever touches the [tokens, 4d]
+                                                activations
+  ``patch_gpt_neo(model)``                     rebinds the forward of every GPTNeoMLP and of the attention projections
+
+Attention itself (causal and local-window softmax) and LayerNorm are still HF's; they are the next pieces of this row.
+No CPU or eager fallback: CPU tensors raise.
+"""
+from __future__ import annotations
+
+import types
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from .ops import _need_cuda, _ptr, _stream, _wgrad_target
+
+ACT_NONE, ACT_GELU_NEW = 0, 1  # FTK_ACT_* in include/ftk.h
+_launches = 0
+
+
+def launch_count() -> int:
+    return _launches
+
+
+def _check(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor]) -> Tuple[int, int, int]:
+    _need_cuda(x, w, b)
+    if x.dtype != torch.bfloat16 or w.dtype != torch.bfloat16 or (b is not None and b.dtype != torch.bfloat16):
+        raise _lib.FtkError("ftk linear layers take bfloat16 activations, weights and biases")
+    if x.dim() != 2 or w.dim() != 2 or x.shape[1] != w.shape[1] or not x.is_contiguous() or not w.is_contiguous():
+        raise _lib.FtkError(f"bad operands: x {tuple(x.shape)} weight {tuple(w.shape)} (contiguous 2-D, shared K)")
+    M, K = x.shape
+    N = w.shape[0]
+    if K % 64 or N % 64:
+        raise _lib.FtkError(f"K={K} and N={N} must be multiples of 64")
+    return M, K, N
+
+
+@torch.library.custom_op("ftk::linear_fwd", mutates_args=())
+def linear_fwd(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor], act: int, save_pre: bool
+               ) -> Tuple[torch.Tensor, torch.Tensor]:
+    """(y, pre): y = act(x @ w.T + b); pre = x @ w.T + b when ``save_pre`` (else empty)."""
+    global _launches
+    M, K, N = _check(x, w, b)
+    y = torch.empty((M, N), dtype=torch.bfloat16, device=x.device)
+    pre = torch.empty((M, N) if save_pre else (0,), dtype=torch.bfloat16, device=x.device)
+    with torch.cuda.device(x.device):
+        rc = _lib.lib().ftk_linear_fwd(x.data_ptr(), w.data_ptr(), _ptr(b), M, K, N, act, y.data_ptr(),
+                                       pre.data_ptr() if save_pre else 0, _stream(x))
+    _lib.check(rc, "ftk_linear_fwd")
+    _launches += 1
+    return y, pre
+
+
+@linear_fwd.register_fake
+def _(x, w, b, act, save_pre):
+    return x.new_empty((x.shape[0], w.shape[0])), x.new_empty((x.shape[0], w.shape[0]) if save_pre else (0,))
+
+
+def _bwd_impl(x, w, dy, mul_pre, need_dx, dw_mode, dW_into, need_db):
+    global _launches
+    M, K, N = _check(x, w, None)
+    _need_cuda(dy, mul_pre)
+    if dy.shape != (M, N) or dy.dtype != torch.bfloat16 or not dy.is_contiguous():
+        raise _lib.FtkError("dy must be a contiguous bfloat16 [M, N] tensor")
+    dev = x.device
+    dx = torch.empty((M, K) if need_dx else (0,), dtype=torch.bfloat16, device=dev)
+    acc = 0
+    if dw_mode == 0:      # no weight gradient
+        dw, code = x.new_empty((0,)), _lib.FTK_BF16
+    elif dW_into is not None:
+        dw, code, acc = dW_into, (_lib.FTK_F32 if dW_into.dtype == torch.float32 else _lib.FTK_BF16), 1
+        if getattr(dW_into, "_ftk_overwrite", False):
+            dW_into._ftk_overwrite, acc = False, 0
+    else:
+        dw, code = torch.empty((N, K), dtype=torch.bfloat16, device=dev), _lib.FTK_BF16
+    db = torch.empty((N,) if need_db else (0,), dtype=torch.float32, device=dev)
+    with torch.cuda.device(dev):
+        rc = _lib.lib().ftk_linear_bwd(x.data_ptr(), w.data_ptr(), dy.data_ptr(), _ptr(mul_pre), M, K, N,
+                                       dx.data_ptr() if need_dx else 0, dw.data_ptr() if dw_mode else 0, code, acc,
+                                       db.data_ptr() if need_db else 0, _stream(x))
+    _lib.check(rc, "ftk_linear_bwd")
+    _launches += int(need_dx) + int(dw_mode != 0) + int(need_db)
+    return dx, dw, db
+
+
+@torch.library.custom_op("ftk::linear_bwd", mutates_args=())
+def linear_bwd(x: torch.Tensor, w: torch.Tensor, dy: torch.Tensor, mul_pre: Optional[torch.Tensor], need_dx: bool,
+               need_dw: bool, need_db: bool) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """(dx, dw, db) of y = x @ w.T + b; dx is multiplied by gelu_new'(mul_pre) when given.  Unwanted ones are empty."""
+    return _bwd_impl(x, w, dy, mul_pre, need_dx, int(need_dw), None, need_db)
+
+
+@linear_bwd.register_fake
+def _(x, w, dy, mul_pre, need_dx, need_dw, need_db):
+    return (x.new_empty(x.shape if need_dx else (0,)), w.new_empty(w.shape if need_dw else (0,)),
+            x.new_empty((w.shape[0],) if need_db else (0,), dtype=torch.float32))
+
+
+@torch.library.custom_op("ftk::linear_bwd_into", mutates_args=("dW_into",))
+def linear_bwd_into(x: torch.Tensor, w: torch.Tensor, dy: torch.Tensor, mul_pre: Optional[torch.Tensor], need_dx: bool,
+                    need_db: bool, dW_into: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``linear_bwd`` with the dW GEMM adding into ``dW_into`` (bf16 or fp32 [N, K]).  Returns (dx, db)."""
+    dx, _, db = _bwd_impl(x, w, dy, mul_pre, need_dx, 2, dW_into, need_db)
+    return dx, db
+
+
+@linear_bwd_into.register_fake
+def _(x, w, dy, mul_pre, need_dx, need_db, dW_into):
+    return x.new_empty(x.shape if need_dx else (0,)), x.new_empty((w.shape[0],) if need_db else (0,), dtype=torch.float32)
+
+
+def _backward(x, w, b, dy, mul_pre, need_dx, need_dw, need_db):
+    """dx, dw (None when it was added into the parameter's gradient buffer in the kernel), db."""
+    into = _wgrad_target(w) if need_dw else None
+    if into is not None:
+        dx, db = torch.ops.ftk.linear_bwd_into(x, w, dy, mul_pre, need_dx, need_db, into)
+        dw = None
+    else:
+        dx, dw, db = torch.ops.ftk.linear_bwd(x, w, dy, mul_pre, need_dx, need_dw, need_db)
+        dw = dw if need_dw else None
+    return (dx if need_dx else None), dw, (db.to(b.dtype) if need_db else None)
+
+
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b):
+        y, _ = torch.ops.ftk.linear_fwd(x, w, b, ACT_NONE, False)
+        ctx.save_for_backward(x, w, b)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w, b = ctx.saved_tensors
+        dx, dw, db = _backward(x, w, b, dy.contiguous(), None, ctx.needs_input_grad[0], ctx.needs_input_grad[1],
+                               b is not None and ctx.needs_input_grad[2])
+        return dx, dw, db
+
+
+class _MlpGeluNew(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w_fc, b_fc, w_proj, b_proj):
+        a, pre = torch.ops.ftk.linear_fwd(x, w_fc, b_fc, ACT_GELU_NEW, True)
+        y, _ = torch.ops.ftk.linear_fwd(a, w_proj, b_proj, ACT_NONE, False)
+        ctx.save_for_backward(x, w_fc, b_fc, w_proj, b_proj, pre, a)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w_fc, b_fc, w_proj, b_proj, pre, a = ctx.saved_tensors
+        ng = ctx.needs_input_grad
+        # c_proj: its dX GEMM hands back d(pre) directly (epilogue multiplies by gelu_new'(pre))
+        dpre, dw_proj, db_proj = _backward(a, w_proj, b_proj, dy.contiguous(), pre, True, ng[3],
+                                           b_proj is not None and ng[4])
+        dx, dw_fc, db_fc = _backward(x, w_fc, b_fc, dpre, None, ng[0], ng[1], b_fc is not None and ng[2])
+        return dx, dw_fc, db_fc, dw_proj, db_proj
+
+
+def linear(x: torch.Tensor, weight: torch.Tensor, bias: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``torch.nn.functional.linear`` for bf16 CUDA tensors on the tcgen05 kernels; any leading dimensions."""
+    lead = x.shape[:-1]
+    y = _Linear.apply(x.reshape(-1, x.shape[-1]).contiguous(), weight, bias)
+    return y.reshape(*lead, weight.shape[0])
+
+
+def mlp_gelu_new(x: torch.Tensor, w_fc: torch.Tensor, b_fc: Optional[torch.Tensor], w_proj: torch.Tensor,
+                 b_proj: Optional[torch.Tensor]) -> torch.Tensor:
+    """``c_proj(gelu_new(c_fc(x)))`` -- HF GPTNeoMLP / GPTJMLP without their dropout (resid_dropout = 0 in both
+    configs) -- as two GEMMs with the bias, the activation and its derivative inside their epilogues."""
+    lead = x.shape[:-1]
+    y = _MlpGeluNew.apply(x.reshape(-1, x.shape[-1]).contiguous(), w_fc, b_fc, w_proj, b_proj)
+    return y.reshape(*lead, w_proj.shape[0])
+
+
+def patch_gpt_neo(model) -> int:
+    """Rebind, in place, the forward of every GPT-Neo MLP (``c_fc`` -> gelu_new -> ``c_proj``) and of the attention's
+    ``q_proj`` / ``k_proj`` / ``v_proj`` / ``out_proj`` to the kernels above.  Parameters, module names and state dict
+    are unchanged.  Returns the number of modules rebound; raises if the model is not a bf16 CUDA GPT-Neo with the
+    gelu_new activation."""
+    cfg = model.config
+    if getattr(cfg, "model_type", "") != "gpt_neo" or getattr(cfg, "activation_function", "") != "gelu_new":
+        raise _lib.FtkError("patch_gpt_neo: expected a GPT-Neo model with activation_function='gelu_new'")
+    n = 0
+    for block in model.base_model.h:
+        mlp = block.mlp
+        if float(getattr(mlp.dropout, "p", 0.0)) != 0.0:
+            raise _lib.FtkError("patch_gpt_neo: resid_dropout must be 0 (the fused MLP has no dropout)")
+
+        def mlp_forward(self, hidden_states):
+            return mlp_gelu_new(hidden_states, self.c_fc.weight, self.c_fc.bias, self.c_proj.weight, self.c_proj.bias)
+
+        mlp.forward = types.MethodType(mlp_forward, mlp)
+        n += 1
+        attn = block.attn.attention
+        for name in ("q_proj", "k_proj", "v_proj", "out_proj"):
+            lin = getattr(attn, name)
+
+            def lin_forward(self, x):
+                return linear(x, self.weight, self.bias)
+
+            lin.forward = types.MethodType(lin_forward, lin)
+            n += 1
+    return n

@@ -1,0 +1,117 @@
+"""Trunk linear layers (first pieces): ftk_linear_fwd / ftk_linear_bwd through the custom ops against
+fp32 CPU torch (the same oracle arithmetic HF's modules run: F.linear, gelu_new), and the patched HF GPT-Neo blocks
+against the unpatched model.  Tolerances as for the hot path: 1e-2 norm-wise on gradients, bf16 inputs."""
+import pytest
+import torch
+
+from oracle import oracle as O
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-2
+
+
+def gelu_new(x):
+    return 0.5 * x * (1.0 + torch.tanh(0.7978845608028654 * (x + 0.044715 * x ** 3)))
+
+
+def _mk(M, K, N, seed, bias=True):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(M, K, generator=g).to(torch.bfloat16)
+    w = (torch.randn(N, K, generator=g) / K ** 0.5).to(torch.bfloat16)
+    b = (torch.randn(N, generator=g) * 0.3).to(torch.bfloat16) if bias else None
+    dy = torch.randn(M, N, generator=g).to(torch.bfloat16)
+    return x, w, b, dy
+
+
+@pytest.mark.parametrize("cg", [1, 2])
+@pytest.mark.parametrize("M,K,N,bias", [(1, 64, 64, True), (300, 128, 192, True), (257, 192, 320, False),
+                                        (1000, 256, 1024, True), (4096, 768, 3072, True)])
+def test_linear_forward_backward(cuda_dev, cta_group, cg, M, K, N, bias):
+    from kubernetes_cloud_b200 import trunk
+    cta_group(cg)
+    x, w, b, dy = _mk(M, K, N, M + N, bias)
+    xr, wr = x.float().requires_grad_(True), w.float().requires_grad_(True)
+    br = b.float().requires_grad_(True) if bias else None
+    yr = torch.nn.functional.linear(xr, wr, br)
+    yr.backward(dy.float())
+    xc, wc = x.cuda().requires_grad_(True), w.cuda().requires_grad_(True)
+    bc = b.cuda().requires_grad_(True) if bias else None
+    y = trunk.linear(xc, wc, bc)
+    y.backward(dy.cuda())
+    torch.cuda.synchronize()
+    assert O.rel_err(y.float(), yr) < RTOL
+    assert O.rel_err(xc.grad.float(), xr.grad) < RTOL and O.rel_err(wc.grad.float(), wr.grad) < RTOL
+    if bias:
+        assert O.rel_err(bc.grad.float(), br.grad) < RTOL
+
+
+@pytest.mark.parametrize("M,d", [(300, 64), (2048, 256), (4096, 768)])
+def test_mlp_gelu_new(cuda_dev, M, d):
+    """c_proj(gelu_new(c_fc(x))): bias + GELU in the first GEMM's epilogue, GELU' in the second one's dX epilogue."""
+    from kubernetes_cloud_b200 import trunk
+    g = torch.Generator().manual_seed(M)
+    x = torch.randn(M, d, generator=g).to(torch.bfloat16)
+    w1 = (torch.randn(4 * d, d, generator=g) / d ** 0.5).to(torch.bfloat16)
+    b1 = (torch.randn(4 * d, generator=g) * 0.3).to(torch.bfloat16)
+    w2 = (torch.randn(d, 4 * d, generator=g) / (4 * d) ** 0.5).to(torch.bfloat16)
+    b2 = (torch.randn(d, generator=g) * 0.3).to(torch.bfloat16)
+    dy = torch.randn(M, d, generator=g).to(torch.bfloat16)
+    ref = [t.float().requires_grad_(True) for t in (x, w1, b1, w2, b2)]
+    yr = torch.nn.functional.linear(gelu_new(torch.nn.functional.linear(ref[0], ref[1], ref[2])), ref[3], ref[4])
+    yr.backward(dy.float())
+    got = [t.cuda().requires_grad_(True) for t in (x, w1, b1, w2, b2)]
+    y = trunk.mlp_gelu_new(*got)
+    y.backward(dy.cuda())
+    torch.cuda.synchronize()
+    assert O.rel_err(y.float(), yr) < RTOL
+    for name, a, r in zip(("dx", "dw_fc", "db_fc", "dw_proj", "db_proj"), got, ref):
+        assert O.rel_err(a.grad.float(), r.grad) < 1.5e-2, name  # the hidden activation is rounded to bf16 once more
+
+
+def test_linear_accumulates_into_main_grad(cuda_dev):
+    from kubernetes_cloud_b200 import trunk
+    x, w, b, dy = _mk(512, 128, 256, 9)
+    wr = w.float().requires_grad_(True)
+    for _ in range(2):
+        torch.nn.functional.linear(x.float(), wr, b.float()).backward(dy.float())
+    wc = w.cuda().requires_grad_(True)
+    wc.main_grad = torch.full((256, 128), 5.0, device="cuda")
+    wc.main_grad._ftk_overwrite = True  # first call overwrites (lazy zero), second adds
+    for _ in range(2):
+        trunk.linear(x.cuda().requires_grad_(True), wc, b.cuda()).backward(dy.cuda())
+    assert wc.grad is None and O.rel_err(wc.main_grad, wr.grad) < 5e-3
+
+
+def test_patched_gpt_neo_matches_the_hf_blocks(cuda_dev):
+    """patch_gpt_neo on a small GPT-Neo (global + local attention layers): same loss and gradients as the unpatched
+    bf16 model on the GPU, and close to the fp32 CPU model."""
+    from transformers import GPTNeoConfig, GPTNeoForCausalLM
+    from kubernetes_cloud_b200 import trunk
+    from kubernetes_cloud_b200.loss import compute_loss
+    torch.manual_seed(1)
+    cfg = GPTNeoConfig(vocab_size=1024, hidden_size=256, num_layers=2, num_heads=4, max_position_embeddings=128,
+                       attention_types=[[["global", "local"], 1]], window_size=32)
+    ref32 = GPTNeoForCausalLM(cfg)
+    ids = torch.randint(0, 1024, (4, 128))
+    mask = torch.ones_like(ids, dtype=torch.bool)
+    out32 = ref32(input_ids=ids, attention_mask=mask, labels=ids)
+    out32.loss.backward()
+    models = []
+    for patched in (False, True):
+        m = GPTNeoForCausalLM(cfg)
+        m.load_state_dict(ref32.state_dict())
+        m = m.cuda().to(torch.bfloat16)
+        m.train()
+        if patched:
+            assert trunk.patch_gpt_neo(m) == 2 * 5
+        inputs = {"input_ids": ids.cuda(), "attention_mask": mask.cuda(), "labels": ids.cuda().clone()}
+        loss = compute_loss(m, inputs)
+        loss.backward()
+        models.append((float(loss.detach()), m))
+    (l0, m0), (l1, m1) = models
+    assert abs(l1 - l0) <= 3e-3 * abs(l0) and abs(l1 - float(out32.loss)) <= 1e-2 * float(out32.loss)
+    for (n0, p0), (n1, p1), (_, p32) in zip(m0.named_parameters(), m1.named_parameters(), ref32.named_parameters()):
+        if p0.grad is None:
+            continue
+        assert O.rel_err(p1.grad.float(), p0.grad.float()) < 5e-2, n0   # bf16 model vs bf16 model
+        assert O.rel_err(p1.grad.float(), p32.grad) < 8e-2, n0          # vs the fp32 CPU model (bf16 trunk noise)

@@ -61,4 +61,16 @@ for slab in (0, 2048, 4096, 5632, 8192, 9216, 16384):
     out[f"fused_slab{slab}"] = {"ms": round(ms, 3), "algorithmic_tflops": round(flops / ms / 1e9, 1),
                                 "rows": L.ftk_lmhead_ce_fused_slab_rows(M, d, V, slab)}
 ops.set_fused_slab_rows(0)
+# per-kernel breakdown of the automatic configuration from the library's launch timeline
+_lib.timeline_enable(True)
+for _ in range(5):
+    fused()
+tl = _lib.timeline_read(with_start=True)
+_lib.timeline_enable(False)
+agg = {}
+for name, ms, _ in tl:
+    agg[name] = agg.get(name, 0.0) + ms / 5
+out["fused_auto_kernels_ms"] = {k: round(v, 3) for k, v in agg.items()}
+per = len(tl) // 5
+out["fused_auto_trace_last_call"] = [(n, round(st - tl[-per][2], 3), round(ms, 3)) for n, ms, st in tl[-per:]]
 print(json.dumps(out))
