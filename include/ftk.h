@@ -94,6 +94,8 @@ int ftk_set_option(int32_t key, int32_t value);
 #define FTK_TL_ALLREDUCE 12 /* the NCCL collective, on the communication stream */
 #define FTK_TL_LINEAR_FWD 13
 #define FTK_TL_LINEAR_DX 14
+#define FTK_TL_ATTN_FWD 15
+#define FTK_TL_ATTN_BWD 16
 int ftk_timeline_enable(int32_t on);
 int ftk_timeline_read(int32_t* tags, float* ms, float* start_ms, int32_t max_n);
 
@@ -280,6 +282,27 @@ int ftk_linear_fwd(const void* X, const void* W, const void* bias, int64_t M, in
                    void* pre, void* stream);
 int ftk_linear_bwd(const void* X, const void* W, const void* dY, const void* dx_mul_pre, int64_t M, int32_t K, int32_t N,
                    void* dX, void* dW, int32_t dw_dtype, int32_t accumulate, float* dbias, void* stream);
+
+/*
+ * Causal / local-window self-attention of the transformer trunk. Replaces HF GPT-Neo's eager
+ * attention (GPTNeoSelfAttention._attn: fp32 Q.K^T, where(causal or sliding-window bias), + attention_mask, softmax,
+ * .V, reached from FT.py:479 model(**inputs) and re-run by gradient checkpointing, FT.py:884) and its autograd.
+ * The [T, T] scores exist only in TMEM.
+ *   Q, K, V, O, dO, dQ, dK, dV   bf16 [B * T, H * head_dim]: the projections' own outputs, heads side by side in a row
+ *   key_mask   uint8 [B * T] (non-zero = this position may be attended) or NULL; 16-byte aligned
+ *   window     0: causal (key j visible from query i iff j <= i); w > 0: also j > i - w (GPT-Neo's local layers, 256)
+ *   scale      multiplies Q.K^T (1 for GPT-Neo, 1/sqrt(head_dim) for GPT-2 / GPT-J)
+ *   lse        fp32 [B * H * T]: natural-log sum-exp of each row's visible scores (+inf for a row that sees no key,
+ *              whose output is 0)
+ *   workspace  ftk_attention_bwd_workspace bytes (the row sums of dO * O)
+ * Requirements: T % 128 == 0, head_dim 64 or 128, 16-byte aligned buffers. Deterministic (no atomics).
+ */
+int ftk_attention_fwd(const void* Q, const void* K, const void* V, const uint8_t* key_mask, int32_t B, int32_t T, int32_t H,
+                      int32_t head_dim, int32_t window, float scale, void* O, float* lse, void* stream);
+size_t ftk_attention_bwd_workspace(int32_t B, int32_t T, int32_t H);
+int ftk_attention_bwd(const void* Q, const void* K, const void* V, const void* O, const void* dO, const float* lse,
+                      const uint8_t* key_mask, int32_t B, int32_t T, int32_t H, int32_t head_dim, int32_t window,
+                      float scale, void* dQ, void* dK, void* dV, void* workspace, size_t workspace_bytes, void* stream);
 
 /*
  * Data-parallel gradient all-reduce (replaces DeepSpeed ZeRO's bucketed

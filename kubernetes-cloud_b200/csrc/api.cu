@@ -30,6 +30,55 @@ int get_device_info(DeviceInfo* out) {
   return FTK_OK;
 }
 
+// ---- TMA tensor maps (shared by the tcgen05 translation units)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static int get_encode_fn(EncodeTiledFn* out) {
+  static EncodeTiledFn cached = nullptr;
+  if (cached == nullptr) {
+    void* fn = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    FTK_CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+    if (qres != cudaDriverEntryPointSuccess || fn == nullptr)
+      return fail(FTK_EUNSUPPORTED, "cuTensorMapEncodeTiled not available from the driver");
+    cached = reinterpret_cast<EncodeTiledFn>(fn);
+  }
+  *out = cached;
+  return FTK_OK;
+}
+
+// bf16 row-major [dim1][dim0] with row pitch pitch_bytes; box = box0 x box1 elements; 128-byte swizzle.
+// Out-of-bounds parts of a box are filled with zeros.
+int make_tmap(CUtensorMap* tm, const void* base, uint64_t dim0, uint64_t dim1, uint64_t pitch_bytes, uint32_t box0,
+              uint32_t box1) {
+  EncodeTiledFn enc = nullptr;
+  if (int rc = get_encode_fn(&enc)) return rc;
+  // cuTensorMapEncodeTiled is a driver call and needs a context current on THIS thread; a thread that has only ever
+  // been handed cached allocations (the autograd engine's thread) may not have one yet.  cudaFree(0) binds the
+  // device's primary context; once per thread.
+  static thread_local bool ctx_bound = false;
+  if (!ctx_bound) {
+    FTK_CUDA_CHECK(cudaFree(nullptr));
+    ctx_bound = true;
+  }
+  FTK_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "tensor base %p is not 16-byte aligned", base);
+  FTK_REQUIRE(pitch_bytes % 16 == 0, "row pitch %llu is not a multiple of 16 bytes",
+              static_cast<unsigned long long>(pitch_bytes));
+  FTK_REQUIRE(box0 * 2 <= 128 && box1 <= 256, "bad TMA box %u x %u", box0, box1);
+  const cuuint64_t dims[2] = {dim0, dim1};
+  const cuuint64_t strides[1] = {pitch_bytes};
+  const cuuint32_t box[2] = {box0, box1};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_L2_256B;  // 64 B / 128 B / none measured the same
+  const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, promo,
+                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fail(FTK_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
+  return FTK_OK;
+}
+
 namespace {
 std::atomic<int> g_options[FTK_OPT_COUNT_] = {{2}, {0}, {0}, {0}};  // cta_group 2, gather auto/auto, no SM reserve
 }

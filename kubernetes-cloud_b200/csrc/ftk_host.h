@@ -1,5 +1,6 @@
 // Host-side helpers shared by the C-ABI translation units: thread-local error text, CUDA checks.
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdarg.h>
 #include <stdio.h>
@@ -37,6 +38,11 @@ struct DeviceInfo {
   int cc_minor;
 };
 int get_device_info(DeviceInfo* out);  // current device; FTK_OK or error
+
+// bf16 row-major [dim1][dim0] tensor map with row pitch pitch_bytes; box = box0 x box1 elements; 128-byte swizzle;
+// out-of-bounds parts of a box read as zeros.  FTK_OK or an error code.
+int make_tmap(CUtensorMap* tm, const void* base, uint64_t dim0, uint64_t dim1, uint64_t pitch_bytes, uint32_t box0,
+              uint32_t box1);
 
 // Launch timeline (ftk_timeline_*): when enabled, a pair of CUDA events brackets every tagged launch on its own
 // stream.  TimelineScope records the first event at construction and the second at destruction.

@@ -990,46 +990,6 @@ __global__ void __launch_bounds__(256) probs_to_dz_kernel(__nv_bfloat16* __restr
 }
 
 // ------------------------------------------------------------------------------------------------ host side
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-int get_encode_fn(EncodeTiledFn* out) {
-  static EncodeTiledFn cached = nullptr;
-  if (cached == nullptr) {
-    void* fn = nullptr;
-    cudaDriverEntryPointQueryResult qres;
-    FTK_CUDA_CHECK(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
-    if (qres != cudaDriverEntryPointSuccess || fn == nullptr)
-      return fail(FTK_EUNSUPPORTED, "cuTensorMapEncodeTiled not available from the driver");
-    cached = reinterpret_cast<EncodeTiledFn>(fn);
-  }
-  *out = cached;
-  return FTK_OK;
-}
-
-// bf16 row-major [dim1][dim0] with row pitch pitch_bytes; box = box0 x box1 elements; 128-byte swizzle.
-// Out-of-bounds parts of a box are filled with zeros.
-int make_tmap(CUtensorMap* tm, const void* base, uint64_t dim0, uint64_t dim1, uint64_t pitch_bytes, uint32_t box0,
-              uint32_t box1) {
-  EncodeTiledFn enc = nullptr;
-  if (int rc = get_encode_fn(&enc)) return rc;
-  FTK_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, "tensor base %p is not 16-byte aligned", base);
-  FTK_REQUIRE(pitch_bytes % 16 == 0, "row pitch %llu is not a multiple of 16 bytes",
-              static_cast<unsigned long long>(pitch_bytes));
-  FTK_REQUIRE(box0 * 2 <= 128 && box1 <= 256, "bad TMA box %u x %u", box0, box1);
-  const cuuint64_t dims[2] = {dim0, dim1};
-  const cuuint64_t strides[1] = {pitch_bytes};
-  const cuuint32_t box[2] = {box0, box1};
-  const cuuint32_t estr[2] = {1, 1};
-  const CUtensorMapL2promotion promo = CU_TENSOR_MAP_L2_PROMOTION_L2_256B;  // 64 B / 128 B / none measured the same
-  const CUresult r = enc(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, estr,
-                         CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, promo,
-                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-  if (r != CUDA_SUCCESS) return fail(FTK_ECUDA, "cuTensorMapEncodeTiled failed with CUresult %d", static_cast<int>(r));
-  return FTK_OK;
-}
-
 // SMs the persistent kernels leave idle (FTK_OPT_SM_RESERVE): room for a concurrent NCCL kernel, whose CTAs cannot
 // share an SM with ours (registers) and would otherwise wait for a whole GEMM to finish.
 inline int sm_reserve() { return ftk::option(FTK_OPT_SM_RESERVE); }

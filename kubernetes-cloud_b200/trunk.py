@@ -11,7 +11,10 @@ tcgen05 kernel template covers, leaving the module tree, parameter names and che
                                                 activations
   ``patch_gpt_neo(model)``                     rebinds the forward of every GPTNeoMLP and of the attention projections
 
-Attention itself (causal and local-window softmax) and LayerNorm are still HF's; they are the next pieces of this row.
+  ``attention(q, k, v, key_mask, heads, window, scale)``   HF's eager fp32 softmax(Q.K^T).V with its causal / sliding-
+                                                window bias                           -> ftk_attention_fwd / _bwd (the [T, T]
+                                                scores never leave TMEM)
+LayerNorm and the residual adds are still torch's; they are the next pieces of this row.
 No CPU or eager fallback: CPU tensors raise.
 """
 from __future__ import annotations
@@ -181,15 +184,119 @@ def mlp_gelu_new(x: torch.Tensor, w_fc: torch.Tensor, b_fc: Optional[torch.Tenso
     return y.reshape(*lead, w_proj.shape[0])
 
 
-def patch_gpt_neo(model) -> int:
-    """Rebind, in place, the forward of every GPT-Neo MLP (``c_fc`` -> gelu_new -> ``c_proj``) and of the attention's
-    ``q_proj`` / ``k_proj`` / ``v_proj`` / ``out_proj`` to the kernels above.  Parameters, module names and state dict
-    are unchanged.  Returns the number of modules rebound; raises if the model is not a bf16 CUDA GPT-Neo with the
-    gelu_new activation."""
+@torch.library.custom_op("ftk::attention_fwd", mutates_args=())
+def attention_fwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, key_mask: Optional[torch.Tensor], B: int, T: int,
+                  H: int, window: int, scale: float) -> Tuple[torch.Tensor, torch.Tensor]:
+    """q, k, v: bf16 [B * T, H * head_dim] (the projections' outputs).  Returns (o, lse fp32 [B * H * T])."""
+    global _launches
+    _need_cuda(q, k, v, key_mask)
+    for t in (q, k, v):
+        if t.dtype != torch.bfloat16 or t.dim() != 2 or t.shape != q.shape or not t.is_contiguous():
+            raise _lib.FtkError("attention operands must be equal-shaped contiguous bfloat16 [B * T, H * head_dim] matrices")
+    if q.shape[0] != B * T or q.shape[1] % H:
+        raise _lib.FtkError(f"attention: operand shape {tuple(q.shape)} does not match B={B} T={T} H={H}")
+    if key_mask is not None and (key_mask.dtype != torch.uint8 or key_mask.numel() != B * T or not key_mask.is_contiguous()):
+        raise _lib.FtkError("attention: key_mask must be a contiguous uint8 tensor with B * T entries")
+    dh = q.shape[1] // H
+    o = torch.empty_like(q)
+    lse = torch.empty((B * H * T,), dtype=torch.float32, device=q.device)
+    with torch.cuda.device(q.device):
+        rc = _lib.lib().ftk_attention_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), _ptr(key_mask), B, T, H, dh, window,
+                                          scale, o.data_ptr(), lse.data_ptr(), _stream(q))
+    _lib.check(rc, "ftk_attention_fwd")
+    _launches += 1
+    return o, lse
+
+
+@attention_fwd.register_fake
+def _(q, k, v, key_mask, B, T, H, window, scale):
+    return torch.empty_like(q), q.new_empty((B * H * T,), dtype=torch.float32)
+
+
+@torch.library.custom_op("ftk::attention_bwd", mutates_args=())
+def attention_bwd(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, o: torch.Tensor, d_o: torch.Tensor,
+                  lse: torch.Tensor, key_mask: Optional[torch.Tensor], B: int, T: int, H: int, window: int, scale: float
+                  ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
+    """(dq, dk, dv) of ``attention_fwd``."""
+    global _launches
+    _need_cuda(q, k, v, o, d_o, lse, key_mask)
+    if d_o.shape != q.shape or d_o.dtype != torch.bfloat16 or not d_o.is_contiguous():
+        raise _lib.FtkError("attention_bwd: d_o must be a contiguous bfloat16 tensor shaped like q")
+    dh = q.shape[1] // H
+    dq, dk, dv = torch.empty_like(q), torch.empty_like(q), torch.empty_like(q)
+    L = _lib.lib()
+    ws_bytes = L.ftk_attention_bwd_workspace(B, T, H)
+    ws = torch.empty((ws_bytes,), dtype=torch.uint8, device=q.device)
+    with torch.cuda.device(q.device):
+        rc = L.ftk_attention_bwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), o.data_ptr(), d_o.data_ptr(), lse.data_ptr(),
+                                 _ptr(key_mask), B, T, H, dh, window, scale, dq.data_ptr(), dk.data_ptr(), dv.data_ptr(),
+                                 ws.data_ptr(), ws_bytes, _stream(q))
+    _lib.check(rc, "ftk_attention_bwd")
+    _launches += 3
+    return dq, dk, dv
+
+
+@attention_bwd.register_fake
+def _(q, k, v, o, d_o, lse, key_mask, B, T, H, window, scale):
+    return torch.empty_like(q), torch.empty_like(q), torch.empty_like(q)
+
+
+class _Attention(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, q, k, v, key_mask, B, T, H, window, scale):
+        o, lse = torch.ops.ftk.attention_fwd(q, k, v, key_mask, B, T, H, window, scale)
+        ctx.save_for_backward(q, k, v, o, lse, key_mask)
+        ctx.cfg = (B, T, H, window, scale)
+        return o
+
+    @staticmethod
+    def backward(ctx, d_o):
+        q, k, v, o, lse, key_mask = ctx.saved_tensors
+        B, T, H, window, scale = ctx.cfg
+        dq, dk, dv = torch.ops.ftk.attention_bwd(q, k, v, o, d_o.contiguous(), lse, key_mask, B, T, H, window, scale)
+        return dq, dk, dv, None, None, None, None, None, None
+
+
+def attention(q: torch.Tensor, k: torch.Tensor, v: torch.Tensor, key_mask: Optional[torch.Tensor], heads: int,
+              window: int = 0, scale: float = 1.0) -> torch.Tensor:
+    """Causal self-attention softmax(scale * Q.K^T + bias).V per head, as HF GPT-Neo's eager ``_attn`` computes it (fp32
+    scores, no 1/sqrt(d) factor there: pass ``scale``).  ``q, k, v``: bf16 [B, T, heads * head_dim], heads side by side
+    as the projections produce them (no split / merge copies); ``key_mask``: bool / uint8 [B, T], False = never
+    attended (padding), or None; ``window`` > 0: sliding window (key j visible from i iff i - window < j <= i).
+    T must be a multiple of 128, head_dim 64 or 128.  Returns [B, T, heads * head_dim]."""
+    B, T, D = q.shape
+    km = None
+    if key_mask is not None:
+        km = key_mask.reshape(B * T).to(torch.uint8).contiguous()
+    o = _Attention.apply(q.reshape(B * T, D).contiguous(), k.reshape(B * T, D).contiguous(),
+                         v.reshape(B * T, D).contiguous(), km, B, T, heads, int(window), float(scale))
+    return o.reshape(B, T, D)
+
+
+def _key_mask_of(attention_mask: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+    """Which keys may be attended, [B, T] bool, from the mask HF hands its attention layers: a 4-D additive float mask
+    (0 = keep, large negative = drop) or a 4-D bool mask (True = keep), already combined with the causal pattern.  The
+    last query row sees every earlier key, so its row is exactly the padding mask."""
+    if attention_mask is None:
+        return None
+    if attention_mask.dim() == 2:
+        return attention_mask.bool()
+    row = attention_mask[:, 0, -1, :]
+    return row if row.dtype == torch.bool else row >= 0
+
+
+def patch_gpt_neo(model, attention_kernels: bool = True) -> int:
+    """Rebind, in place, the forward of every GPT-Neo MLP (``c_fc`` -> gelu_new -> ``c_proj``), of the attention's
+    ``q_proj`` / ``k_proj`` / ``v_proj`` / ``out_proj`` and (``attention_kernels``) of the self-attention itself to the
+    kernels above.  Parameters, module names and state dict are unchanged.  Returns the number of modules rebound;
+    raises if the model is not a bf16 CUDA GPT-Neo with the gelu_new activation.  The attention kernels need the
+    sequence length to be a multiple of 128 and no attention dropout; other lengths raise at call time."""
     cfg = model.config
     if getattr(cfg, "model_type", "") != "gpt_neo" or getattr(cfg, "activation_function", "") != "gelu_new":
         raise _lib.FtkError("patch_gpt_neo: expected a GPT-Neo model with activation_function='gelu_new'")
     n = 0
+    if attention_kernels:
+        cfg.use_cache = False  # as the reference sets it for training (FT.py:888); the fused attention keeps no KV cache
     for block in model.base_model.h:
         mlp = block.mlp
         if float(getattr(mlp.dropout, "p", 0.0)) != 0.0:
@@ -208,5 +315,20 @@ def patch_gpt_neo(model) -> int:
                 return linear(x, self.weight, self.bias)
 
             lin.forward = types.MethodType(lin_forward, lin)
+            n += 1
+        if attention_kernels:
+            if float(getattr(attn.attn_dropout, "p", 0.0)) != 0.0 or float(getattr(attn.resid_dropout, "p", 0.0)) != 0.0:
+                raise _lib.FtkError("patch_gpt_neo: attention_dropout and resid_dropout must be 0")
+            window = int(cfg.window_size) if attn.attention_type == "local" else 0
+
+            def attn_forward(self, hidden_states, attention_mask=None, layer_past=None, use_cache=False,
+                             output_attentions=False, _window=window, **kwargs):
+                if layer_past is not None or use_cache or output_attentions:
+                    raise _lib.FtkError("the fused attention serves training steps only (no KV cache, no attention maps)")
+                q, k, v = self.q_proj(hidden_states), self.k_proj(hidden_states), self.v_proj(hidden_states)
+                o = attention(q, k, v, _key_mask_of(attention_mask), self.num_heads, _window, 1.0)  # GPT-Neo: no scale
+                return self.out_proj(o), None
+
+            attn.forward = types.MethodType(attn_forward, attn)
             n += 1
     return n

@@ -82,6 +82,52 @@ def test_linear_accumulates_into_main_grad(cuda_dev):
     assert wc.grad is None and O.rel_err(wc.main_grad, wr.grad) < 5e-3
 
 
+def attention_reference(q, k, v, key_mask, H, window, scale):
+    """HF GPT-Neo's eager ``_attn`` restated in fp32 torch on [B, T, H * dh] operands (modeling_gpt_neo.py: fp32 Q.K^T,
+    where(causal / sliding-window bias, s, finfo.min), + additive padding mask, softmax, .V)."""
+    B, T, D = q.shape
+    dh = D // H
+    qh, kh, vh = (t.float().view(B, T, H, dh).permute(0, 2, 1, 3) for t in (q, k, v))
+    s = torch.matmul(qh, kh.transpose(-1, -2)) * scale
+    bias = torch.tril(torch.ones(T, T, dtype=torch.bool))
+    if window > 0:
+        bias = torch.bitwise_xor(bias, torch.tril(bias, -window))
+    s = torch.where(bias, s, torch.tensor(torch.finfo(torch.float32).min))
+    if key_mask is not None:
+        s = s + (~key_mask)[:, None, None, :].float() * torch.finfo(torch.float32).min
+    o = torch.matmul(torch.softmax(s, -1), vh)
+    return o.permute(0, 2, 1, 3).reshape(B, T, D)
+
+
+@pytest.mark.parametrize("B,T,H,dh,window,scale,masked", [(1, 128, 1, 64, 0, 1.0, False), (2, 256, 2, 64, 0, 1.0, False),
+                                                           (2, 384, 2, 128, 0, 0.125, True), (1, 512, 3, 64, 200, 1.0, False),
+                                                           (2, 512, 2, 128, 256, 1.0, True), (1, 256, 2, 128, 64, 1.0, False)])
+def test_attention_forward_backward(cuda_dev, B, T, H, dh, window, scale, masked):
+    """Causal and sliding-window attention against the fp32 restatement of HF's eager path: output and dQ / dK / dV.
+    The padded positions (trailing keys of the last sequence) are excluded from the comparison, as the loss ignores
+    them."""
+    from kubernetes_cloud_b200 import trunk
+    g = torch.Generator().manual_seed(T + dh + window)
+    q, k, v, d_o = ((torch.randn(B, T, H * dh, generator=g) * s).to(torch.bfloat16) for s in (0.5, 0.5, 1.0, 1.0))
+    key_mask = None
+    if masked:
+        key_mask = torch.ones(B, T, dtype=torch.bool)
+        key_mask[-1, T - 37:] = False
+    ref = [t.float().requires_grad_(True) for t in (q, k, v)]
+    o_ref = attention_reference(*ref, key_mask, H, window, scale)
+    keep = torch.ones(B, T, 1) if key_mask is None else key_mask[:, :, None].float()  # padded queries get no gradient
+    o_ref.backward(d_o.float() * keep)
+    got = [t.cuda().requires_grad_(True) for t in (q, k, v)]
+    o = trunk.attention(*got, None if key_mask is None else key_mask.cuda(), H, window, scale)
+    o.backward((d_o.float() * keep).to(torch.bfloat16).cuda())
+    torch.cuda.synchronize()
+    assert torch.isfinite(o).all()
+    assert O.rel_err(o.float().cpu() * keep, o_ref * keep) < RTOL
+    for name, a, r in zip(("dq", "dk", "dv"), got, ref):
+        assert torch.isfinite(a.grad).all(), name
+        assert O.rel_err(a.grad.float().cpu() * keep, r.grad * keep) < 1.5e-2, name
+
+
 def test_patched_gpt_neo_matches_the_hf_blocks(cuda_dev):
     """patch_gpt_neo on a small GPT-Neo (global + local attention layers): same loss and gradients as the unpatched
     bf16 model on the GPU, and close to the fp32 CPU model."""
@@ -103,7 +149,7 @@ def test_patched_gpt_neo_matches_the_hf_blocks(cuda_dev):
         m = m.cuda().to(torch.bfloat16)
         m.train()
         if patched:
-            assert trunk.patch_gpt_neo(m) == 2 * 5
+            assert trunk.patch_gpt_neo(m) == 2 * 6  # per block: MLP, four projections, the attention itself
         inputs = {"input_ids": ids.cuda(), "attention_mask": mask.cuda(), "labels": ids.cuda().clone()}
         loss = compute_loss(m, inputs)
         loss.backward()

@@ -43,9 +43,9 @@ def step(fused: bool):
 out = {"arch": arch, "batch": B, "ctx": T, "tokens": B * T}
 variants = [("hf_lm_head_and_loss", False), ("fused_lm_head_ce", True)]
 if model.config.model_type == "gpt_neo":
-    variants.append(("fused_lm_head_ce_and_ftk_linears", True))  # + trunk.patch_gpt_neo: MLP and projections on our GEMMs
+    variants.append(("fused_lm_head_ce_and_ftk_trunk", True))  # + trunk.patch_gpt_neo: MLP, projections and attention on our kernels
 for name, fused in variants:
-    if name.endswith("ftk_linears"):
+    if name.endswith("ftk_trunk"):
         from kubernetes_cloud_b200 import trunk
         out["modules_rebound"] = trunk.patch_gpt_neo(model)
     torch.cuda.empty_cache()
