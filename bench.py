@@ -603,6 +603,8 @@ def main_gpu(args) -> None:
         line["exposed_comm_ms_per_step"] = exposed_comm_ms
         line["allreduce_max_rel_err"] = allreduce_err
         line["full_gradient_allreduce"] = full_grad
+    if world == 1 and not args.no_full_step:
+        line["full_step"] = run_full_step(dev)
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = run_cpu_baseline()
     print(json.dumps(line), file=RESULT_OUT, flush=True)
@@ -612,6 +614,58 @@ def main_gpu(args) -> None:
         if allreduce_err is None or not (allreduce_err <= tol):
             print(f"all-reduce check failed: max relative error {allreduce_err} > {tol}", file=sys.stderr)
             sys.exit(3)
+
+
+def run_full_step(dev) -> dict:
+    """Context for the headline: one whole finetune step of GPT-Neo-1.3B (BASELINE configs[2]: ctx 2048, batch 8, bf16,
+    gradient checkpointing as the reference enables it, torch fused AdamW) on this GPU, with HF's eager blocks + HF's
+    lm_head/loss, and with this package's fused loss + trunk kernels (patch_gpt_neo).  tokens/s/GPU of the metric's
+    first half.  Errors are reported, not raised: this block must not take the bench line down."""
+    import torch
+    try:
+        from kubernetes_cloud_b200 import trunk
+        from kubernetes_cloud_b200.finetune import load_model
+        from kubernetes_cloud_b200.loss import compute_loss
+        torch.manual_seed(42)
+        model = load_model("gpt-neo-1.3b").to(dev).to(torch.bfloat16)
+        model.train()
+        model.gradient_checkpointing_enable()
+        B, T = BATCH, CTX
+        g = torch.Generator(device=dev).manual_seed(1)
+        ids = torch.randint(0, model.config.vocab_size, (B, T), device=dev, generator=g)
+        mask = torch.ones(B, T, dtype=torch.bool, device=dev)
+        opt = torch.optim.AdamW(model.parameters(), lr=1e-5, fused=True)
+
+        def step(ours: bool):
+            opt.zero_grad(set_to_none=True)
+            if ours:
+                loss = compute_loss(model, {"input_ids": ids, "attention_mask": mask, "labels": ids.clone()})
+            else:
+                loss = model(input_ids=ids, attention_mask=mask, labels=ids).loss
+            loss.backward()
+            opt.step()
+            return loss
+
+        out = {"model": "GPT-Neo-1.3B, ctx 2048, batch 8, bf16, gradient checkpointing, torch fused AdamW",
+               "tokens_per_step": B * T}
+        for name, ours, n in (("hf_eager", False, 2), ("ftk_loss_and_trunk", True, 5)):
+            if ours:
+                out["modules_rebound"] = trunk.patch_gpt_neo(model)
+            for _ in range(2):
+                step(ours)
+            torch.cuda.synchronize(dev)
+            t0 = time.time()
+            for _ in range(n):
+                loss = step(ours)
+            torch.cuda.synchronize(dev)
+            dt = (time.time() - t0) / n
+            out[name] = {"ms_per_step": dt * 1e3, "tokens_per_s_per_gpu": B * T / dt, "loss": float(loss.detach())}
+        out["speedup"] = out["hf_eager"]["ms_per_step"] / out["ftk_loss_and_trunk"]["ms_per_step"]
+        del model, opt
+        torch.cuda.empty_cache()
+        return out
+    except Exception as e:  # noqa: BLE001
+        return {"error": f"{type(e).__name__}: {e}"}
 
 
 def _claim_stdout():
@@ -631,6 +685,7 @@ if __name__ == "__main__":
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-full-step", action="store_true", help="skip the whole-model context block (GPT-Neo-1.3B)")
     a = ap.parse_args()
     if a.impl == "reference":
         main_reference(a)

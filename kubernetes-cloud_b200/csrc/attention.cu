@@ -54,6 +54,11 @@ __device__ __forceinline__ bool visible(int qi, int kj, int window) {
   return kj <= qi && (window <= 0 || kj > qi - window);
 }
 
+// Does every query of block qb see every key of block kb (so that no per-element test is needed)?
+__device__ __forceinline__ bool tile_all_visible(int qb, int kb, int window, const uint8_t* mrow) {
+  return mrow == nullptr && kb * QB + QB - 1 <= qb * QB && (window <= 0 || kb * QB > qb * QB + QB - 1 - window);
+}
+
 // First / last key block a query block needs, and first / last query block a key block is seen by (T % 128 == 0).
 __device__ __forceinline__ void kv_range(int qb, int window, int& lo, int& hi) {
   hi = qb;
@@ -140,7 +145,13 @@ __device__ __forceinline__ void put8_mnmajor(uint8_t* tile, int r, int c0, const
 
 // The visible-and-unmasked test for 32 consecutive keys of one query row, folded into the scores:
 // v[j] = scale * log2(e) * s  (so that exp2 can be used), or -inf where the key must not be attended.
-__device__ __forceinline__ void mask_scores(float* v, int qi, int key0, const AttnParams& p, const uint8_t* mrow, float sl2) {
+__device__ __forceinline__ void mask_scores(float* v, int qi, int key0, const AttnParams& p, const uint8_t* mrow, float sl2,
+                                            bool all_visible) {
+  if (all_visible) {  // a tile wholly inside the causal / window band of every row of the block, no padding mask
+#pragma unroll
+    for (int j = 0; j < 32; ++j) v[j] *= sl2;
+    return;
+  }
   uint32_t mbits = 0xffffffffu;
   if (mrow != nullptr) {
     const uint4 m0 = *reinterpret_cast<const uint4*>(mrow + key0), m1 = *reinterpret_cast<const uint4*>(mrow + key0 + 16);
@@ -184,6 +195,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   const int row0 = b * p.T + qb * QB;  // first row of this block in the [batch * T] matrices
   const int col0 = h * DH;
   const bool issuer = (warp == 4 && lane == 0);
+  // Lanes 1-31 of the issuing warp take no part in mbarrier waits: spinning beside the one lane that has to issue
+  // the work the barrier is waiting for starves it.  They only join the __syncthreads.
+  const bool waits = (warp < 4 || lane == 0);
 
   if (issuer) {
     tma_prefetch_desc(&tmQ);
@@ -226,7 +240,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   const float sl2 = p.scale * kLog2e;
   float m = -INFINITY, l = 0.f, lse2 = 0.f;  // running max / sum in the exp2 domain; lse2 = log2-sum-exp
   uint32_t ph_s = 0, ph_o = 0;
-  mbar_wait(bar_q, 0);
+  if (waits) mbar_wait(bar_q, 0);
 
   for (int t = 0; t < n_tiles; ++t) {
     const int pass = t >= nj, j = j_lo + (pass ? t - nj : t), bufi = t & 1;
@@ -237,7 +251,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       mma_kk<DH>(tmem_s, sQ, sK + bufi * L::TILE, 128, false);
       umma_commit<1>(bar_s);
     }
-    mbar_wait(bar_s, ph_s);
+    if (waits) mbar_wait(bar_s, ph_s);
     ph_s ^= 1;
     tc_fence_after();
     if (warp < 4) {
@@ -248,7 +262,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
           float v[32];
           tmem_ld32(taddr + c * 32, v);
           tmem_ld_wait();
-          mask_scores(v, qi, j * QB + c * 32, p, mrow, sl2);
+          mask_scores(v, qi, j * QB + c * 32, p, mrow, sl2, tile_all_visible(qb, j, p.window, mrow));
           float cm = v[0];
 #pragma unroll
           for (int e = 1; e < 32; ++e) cm = fmaxf(cm, v[e]);
@@ -271,7 +285,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
           float v[32];
           tmem_ld32(taddr + c * 32, v);
           tmem_ld_wait();
-          mask_scores(v, qi, j * QB + c * 32, p, mrow, sl2);
+          mask_scores(v, qi, j * QB + c * 32, p, mrow, sl2, tile_all_visible(qb, j, p.window, mrow));
 #pragma unroll
           for (int q8 = 0; q8 < 4; ++q8) {
             uint32_t w[4];
@@ -292,7 +306,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         mma_k_mn<DH>(tmem_o, sP, sV + bufi * L::TILE, t != nj);  // first tile of pass 1 overwrites
         umma_commit<1>(bar_o);
       }
-      mbar_wait(bar_o, ph_o);  // P, K and V of this tile are free again; O is up to date
+      if (waits) mbar_wait(bar_o, ph_o);  // P, K and V of this tile are free again; O is up to date
       ph_o ^= 1;
       tc_fence_after();
     }
@@ -361,14 +375,15 @@ struct BwdSmem {
 // lse2 = log2-sum-exp of the row, dl = delta of the row.  kKMajor: layout of the dS tile (see put8_*).
 template <bool kWriteP, bool kKMajor>
 __device__ __forceinline__ void tile_p_ds(uint32_t taddr_s, uint32_t taddr_dp, int r, int qi, int key0, const AttnParams& p,
-                                          const uint8_t* mrow, float sl2, float lse2, float dl, uint8_t* sP, uint8_t* sDS) {
+                                          const uint8_t* mrow, float sl2, float lse2, float dl, uint8_t* sP, uint8_t* sDS,
+                                          bool all_visible) {
 #pragma unroll 1
   for (int c = 0; c < 4; ++c) {
     float v[32], g[32];
     tmem_ld32(taddr_s + c * 32, v);
     tmem_ld32(taddr_dp + c * 32, g);
     tmem_ld_wait();
-    mask_scores(v, qi, key0 + c * 32, p, mrow, sl2);
+    mask_scores(v, qi, key0 + c * 32, p, mrow, sl2, all_visible);
 #pragma unroll
     for (int q8 = 0; q8 < 4; ++q8) {
       uint32_t wp[4], wd[4];
@@ -414,6 +429,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   const int kb = blockIdx.x, bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
   const int col0 = h * DH, n_blk = p.T / QB;
   const bool issuer = (warp == 4 && lane == 0);
+  // Lanes 1-31 of the issuing warp take no part in mbarrier waits: spinning beside the one lane that has to issue
+  // the work the barrier is waiting for starves it.  They only join the __syncthreads.
+  const bool waits = (warp < 4 || lane == 0);
   if (issuer) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmK);
@@ -445,7 +463,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
   const float sl2 = p.scale * kLog2e;
   uint32_t ph = 0;
-  mbar_wait(bar_kv, 0);
+  if (waits) mbar_wait(bar_kv, 0);
 
   for (int i = i_lo; i <= i_hi; ++i) {
     if (issuer) {
@@ -458,7 +476,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       mma_kk<DH>(tmem_dp, sDO, sV, 128, false);   // dP = dO_i . V^T
       umma_commit<1>(bar_s);
     }
-    mbar_wait(bar_s, ph);
+    if (waits) mbar_wait(bar_s, ph);
     tc_fence_after();
     if (warp < 4) {
       const int qi = i * QB + r;
@@ -467,7 +485,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       const float lse2 = lse * kLog2e;  // +inf for a row that saw no key: every p is 0
       const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
       tile_p_ds<true, false>(tmem_s + lane_off, tmem_dp + lane_off, r, qi, kb * QB, p, mrow, sl2, lse2, p.delta[sidx], sP,
-                             sDS);
+                             sDS, tile_all_visible(i, kb, p.window, mrow));
     }
     tc_fence_before();
     __syncthreads();
@@ -477,7 +495,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       mma_mn_mn<DH>(tmem_dk, sDS, sQ, i != i_lo);  // dK += dS^T . Q_i
       umma_commit<1>(bar_o);
     }
-    mbar_wait(bar_o, ph);
+    if (waits) mbar_wait(bar_o, ph);
     tc_fence_after();
     ph ^= 1;
   }
@@ -534,6 +552,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   const int qb = blockIdx.x, bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
   const int col0 = h * DH;
   const bool issuer = (warp == 4 && lane == 0);
+  // Lanes 1-31 of the issuing warp take no part in mbarrier waits: spinning beside the one lane that has to issue
+  // the work the barrier is waiting for starves it.  They only join the __syncthreads.
+  const bool waits = (warp < 4 || lane == 0);
   if (issuer) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmK);
@@ -571,7 +592,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     dl = p.delta[sidx];
   }
   uint32_t ph = 0;
-  mbar_wait(bar_q, 0);
+  if (waits) mbar_wait(bar_q, 0);
 
   for (int j = j_lo; j <= j_hi; ++j) {
     if (issuer) {
@@ -584,11 +605,12 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       mma_kk<DH>(tmem_dp, sDO, sV, 128, false);  // dP = dO . V_j^T
       umma_commit<1>(bar_s);
     }
-    mbar_wait(bar_s, ph);
+    if (waits) mbar_wait(bar_s, ph);
     tc_fence_after();
     if (warp < 4) {
       const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
-      tile_p_ds<false, true>(tmem_s + lane_off, tmem_dp + lane_off, r, qi, j * QB, p, mrow, sl2, lse2, dl, nullptr, sDS);
+      tile_p_ds<false, true>(tmem_s + lane_off, tmem_dp + lane_off, r, qi, j * QB, p, mrow, sl2, lse2, dl, nullptr, sDS,
+                             tile_all_visible(qb, j, p.window, mrow));
     }
     tc_fence_before();
     __syncthreads();
@@ -597,7 +619,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       mma_k_mn<DH>(tmem_dq, sDS, sK, j != j_lo);  // dQ += dS . K_j
       umma_commit<1>(bar_o);
     }
-    mbar_wait(bar_o, ph);
+    if (waits) mbar_wait(bar_o, ph);
     tc_fence_after();
     ph ^= 1;
   }

@@ -155,6 +155,9 @@ def build_parser() -> DashParser:
     p.add_argument("--max-steps", type=int, default=-1, help="stop after this many optimizer steps")
     p.add_argument("--max-grad-norm", type=float, default=1.0)
     p.add_argument("--report-json", type=str, default="", help="write per-step metrics here")
+    p.add_argument("--no-ftk-trunk", action=FuzzyBool, dest="ftk_trunk", default=True,
+                   help="keep HF's eager GPT-Neo blocks; by default their MLP, projections and attention run on this "
+                        "package's kernels (trunk.patch_gpt_neo) when the context size is a multiple of 128")
     return p
 
 
@@ -237,6 +240,14 @@ def main(argv: Optional[List[str]] = None) -> dict:
     model.train()  # FT.py:831
     if hasattr(model, "gradient_checkpointing_enable"):
         model.gradient_checkpointing_enable()  # FT.py:884
+    if (args.ftk_trunk and getattr(model.config, "model_type", "") == "gpt_neo" and model.config.hidden_size % 64 == 0
+            and getattr(model.config, "activation_function", "") == "gelu_new"):
+        from . import trunk
+        # the attention kernels additionally need head_dim 64 / 128 and a context that is a multiple of 128
+        attn_ok = args.context_size % 128 == 0 and model.config.hidden_size // model.config.num_heads in (64, 128)
+        n_mod = trunk.patch_gpt_neo(model, attention_kernels=attn_ok)
+        if main_proc:
+            logger.info("TRUNK: %d GPT-Neo modules rebound to the tcgen05 linear / MLP / attention kernels", n_mod)
     if rep.max_token >= model.config.vocab_size:
         raise SystemExit(f"token id {rep.max_token} does not fit the model's vocabulary {model.config.vocab_size}")
 

@@ -285,7 +285,7 @@ def _key_mask_of(attention_mask: Optional[torch.Tensor]) -> Optional[torch.Tenso
     return row if row.dtype == torch.bool else row >= 0
 
 
-def patch_gpt_neo(model, attention_kernels: bool = True) -> int:
+def patch_gpt_neo(model, attention_kernels: Optional[bool] = None) -> int:
     """Rebind, in place, the forward of every GPT-Neo MLP (``c_fc`` -> gelu_new -> ``c_proj``), of the attention's
     ``q_proj`` / ``k_proj`` / ``v_proj`` / ``out_proj`` and (``attention_kernels``) of the self-attention itself to the
     kernels above.  Parameters, module names and state dict are unchanged.  Returns the number of modules rebound;
@@ -294,6 +294,13 @@ def patch_gpt_neo(model, attention_kernels: bool = True) -> int:
     cfg = model.config
     if getattr(cfg, "model_type", "") != "gpt_neo" or getattr(cfg, "activation_function", "") != "gelu_new":
         raise _lib.FtkError("patch_gpt_neo: expected a GPT-Neo model with activation_function='gelu_new'")
+    if cfg.hidden_size % 64 or getattr(cfg, "intermediate_size", None) not in (None, 4 * cfg.hidden_size):
+        raise _lib.FtkError("patch_gpt_neo: hidden_size must be a multiple of 64 (and the MLP 4x as wide)")
+    head_dim = cfg.hidden_size // cfg.num_heads
+    if attention_kernels is None:  # the attention kernels exist for head_dim 64 and 128; other sizes keep HF's attention
+        attention_kernels = head_dim in (64, 128)
+    elif attention_kernels and head_dim not in (64, 128):
+        raise _lib.FtkError(f"patch_gpt_neo: the attention kernels need head_dim 64 or 128, not {head_dim}")
     n = 0
     if attention_kernels:
         cfg.use_cache = False  # as the reference sets it for training (FT.py:888); the fused attention keeps no KV cache

@@ -63,3 +63,28 @@ def test_finetune_cli_short_epoch_tail_and_auto_batch_size(cuda_dev, tmp_path):
     assert out["history"][0]["loss"] != out["history"][2]["loss"]  # second epoch: reshuffled order, updated weights
     out = main(base + ["--gradients", "8", "--max-steps", "1"])     # --bs defaults to -1; 7 contexts < bs * gradients
     assert out["steps"] == 1 and math.isfinite(out["history"][0]["loss"])
+
+
+def test_finetune_cli_on_the_ftk_trunk(cuda_dev, tmp_path):
+    """GPT-Neo with head_dim 64 at a context of 128: the command line rebinds MLP, projections and attention to this
+    package's kernels (global + sliding-window layers).  Same first-step loss as HF's eager blocks (--no-ftk-trunk),
+    and it learns."""
+    from transformers import GPTNeoConfig
+    from kubernetes_cloud_b200 import write_token_file
+    from kubernetes_cloud_b200.finetune import main
+    T, V = 128, 512
+    cfg_dir = tmp_path / "tiny"
+    cfg_dir.mkdir()
+    GPTNeoConfig(vocab_size=V, hidden_size=128, num_layers=2, num_heads=2, max_position_embeddings=T,
+                 attention_types=[[["global", "local"], 1]], window_size=48).save_pretrained(str(cfg_dir))
+    pattern = np.random.default_rng(0).integers(0, V - 1, size=37)
+    path = str(tmp_path / "d.tokens")
+    write_token_file(path, np.tile(pattern, 40 * T // 37 + 1)[: 40 * T - 9], T, pad_id=V - 1)
+    argv = ["--run-name", "t", "--model", str(cfg_dir), "--dataset", path, "--context-size", str(T), "--bs", "4",
+            "--gradients", "2", "--lr", "3e-3", "--max-steps", "10", "--pad-token-id", str(V - 1), "--eos-token-id",
+            str(V - 1)]
+    ours = main(argv)["history"]
+    eager = main(argv + ["--no-ftk-trunk"])["history"]
+    assert all(math.isfinite(h["loss"]) for h in ours)
+    assert abs(ours[0]["loss"] - eager[0]["loss"]) <= 5e-3 * eager[0]["loss"]
+    assert ours[-1]["loss"] < ours[0]["loss"] - 0.5 and abs(ours[-1]["loss"] - eager[-1]["loss"]) < 0.3

@@ -59,6 +59,17 @@ for name, fused in variants:
         loss = step(fused)
     torch.cuda.synchronize()
     dt = (time.time() - t0) / n
-    out[name] = {"ms_per_step": round(dt * 1e3, 2), "tokens_per_s": round(B * T / dt), "loss": round(float(loss), 4),
+    out[name] = {"ms_per_step": round(dt * 1e3, 2), "tokens_per_s": round(B * T / dt), "loss": round(float(loss.detach()), 4),
                  "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 1e9, 2)}
+    if fused:  # where this library's kernels spend the step (launch timeline of one more step)
+        from kubernetes_cloud_b200 import _lib
+        _lib.timeline_enable(True)
+        step(fused)
+        torch.cuda.synchronize()
+        agg = {}
+        for kname, ms in _lib.timeline_read():
+            agg[kname] = agg.get(kname, 0.0) + ms
+        _lib.timeline_enable(False)
+        out[name]["ftk_kernels_ms"] = {k: round(v, 2) for k, v in sorted(agg.items(), key=lambda kv: -kv[1])}
+        out[name]["ftk_kernels_total_ms"] = round(sum(v for k, v in agg.items() if k != "convert"), 2)
 print(json.dumps(out))
