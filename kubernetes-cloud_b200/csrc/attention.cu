@@ -30,7 +30,12 @@ namespace {
 using namespace ftk;
 
 constexpr int QB = 128;            // rows of a block (queries or keys) = TMEM lanes
-constexpr int kAttnThreads = 160;  // warps 0-3: one accumulator row per thread; warp 4: TMA + MMA issue, TMEM allocation
+// Warps 0-7: row threads.  Thread t owns accumulator row t % 128 (warp w reads TMEM lanes 32 * (w % 4)) and the column
+// half t / 128 of every tile, so each row is worked on by two threads on the same SM sub-partition: with a single warp
+// per scheduler nothing hid the TMEM-load and MUFU latencies (ncu: issue slots 22 % busy, tensor pipe 15 %).
+// Warp 8: TMA + MMA issue (lane 0), TMEM allocation.
+constexpr int kAttnThreads = 288;
+constexpr int kIssuerWarp = 8;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
 
@@ -170,7 +175,8 @@ template <int DH>
 struct FwdSmem {
   static constexpr uint32_t TILE = QB * DH * 2;  // one [128 x DH] bf16 operand tile
   static constexpr uint32_t Q_OFF = 0, K_OFF = TILE, V_OFF = 3 * TILE, P_OFF = 5 * TILE, BAR_OFF = P_OFF + 32768;
-  static constexpr uint32_t BYTES = 1024 + BAR_OFF + 8 * 8 + 16;
+  static constexpr uint32_t STAT_OFF = BAR_OFF + 128;  // [2][256] floats: the two column halves' softmax statistics
+  static constexpr uint32_t BYTES = 1024 + STAT_OFF + 2048;
 };
 
 template <int DH>
@@ -189,15 +195,17 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   uint64_t* bar_s = bar_kv + 3;
   uint64_t* bar_o = bar_kv + 4;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_kv + 5);
+  float* stat_m = reinterpret_cast<float*>(smem + L::STAT_OFF);
+  float* stat_l = stat_m + 256;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qb = blockIdx.x, bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
   const int row0 = b * p.T + qb * QB;  // first row of this block in the [batch * T] matrices
   const int col0 = h * DH;
-  const bool issuer = (warp == 4 && lane == 0);
+  const bool issuer = (warp == kIssuerWarp && lane == 0);
   // Lanes 1-31 of the issuing warp take no part in mbarrier waits: spinning beside the one lane that has to issue
   // the work the barrier is waiting for starves it.  They only join the __syncthreads.
-  const bool waits = (warp < 4 || lane == 0);
+  const bool waits = (warp < kIssuerWarp || lane == 0);
 
   if (issuer) {
     tma_prefetch_desc(&tmQ);
@@ -210,7 +218,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     mbar_init(bar_o, 1);
     fence_mbar_init();
   }
-  if (warp == 4) {
+  if (warp == kIssuerWarp) {
     tmem_alloc<1>(tmem_slot, 256);
     tmem_relinquish<1>();
   }
@@ -234,7 +242,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     issue_load(0);
   }
 
-  const int r = threadIdx.x;            // row threads: r < 128
+  const int r = threadIdx.x & 127, half = threadIdx.x >> 7;  // row threads: accumulator row and column half
   const int qi = qb * QB + r;           // position of this thread's query inside its sequence
   const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
   const float sl2 = p.scale * kLog2e;
@@ -251,14 +259,14 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       mma_kk<DH>(tmem_s, sQ, sK + bufi * L::TILE, 128, false);
       umma_commit<1>(bar_s);
     }
-    if (waits) mbar_wait(bar_s, ph_s);
+    if (waits) mbar_wait_poll(bar_s, ph_s);
     ph_s ^= 1;
     tc_fence_after();
-    if (warp < 4) {
-      const uint32_t taddr = tmem_s + (static_cast<uint32_t>(warp * 32) << 16);
+    if (warp < kIssuerWarp) {
+      const uint32_t taddr = tmem_s + (static_cast<uint32_t>((warp & 3) * 32) << 16);
       if (pass == 0) {
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 2 * half; c < 2 * half + 2; ++c) {
           float v[32];
           tmem_ld32(taddr + c * 32, v);
           tmem_ld_wait();
@@ -275,13 +283,13 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
             m = mn;
           }
         }
-        if (t == nj - 1) {
-          lse2 = (m == -INFINITY) ? INFINITY : m + log2f(l);  // a row that sees no key: every p becomes 0
-          p.lse[static_cast<size_t>(bh) * p.T + qi] = (m == -INFINITY) ? INFINITY : lse2 * kLn2;
+        if (t == nj - 1) {  // end of pass 0: publish this column half's statistics of the row
+          stat_m[threadIdx.x] = m;
+          stat_l[threadIdx.x] = l;
         }
       } else {
 #pragma unroll 1
-        for (int c = 0; c < 4; ++c) {
+        for (int c = 2 * half; c < 2 * half + 2; ++c) {
           float v[32];
           tmem_ld32(taddr + c * 32, v);
           tmem_ld_wait();
@@ -300,23 +308,32 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     }
     tc_fence_before();
     __syncthreads();
+    if (t == nj - 1 && warp < kIssuerWarp) {  // merge the two halves: log2-sum-exp of the whole row
+      const float m0 = stat_m[r], m1 = stat_m[r + 128], mm = fmaxf(m0, m1);
+      if (mm == -INFINITY) {
+        lse2 = INFINITY;  // a row that sees no key: every p becomes 0
+      } else {
+        lse2 = mm + log2f(stat_l[r] * fast_exp2(m0 - mm) + stat_l[r + 128] * fast_exp2(m1 - mm));
+      }
+      if (half == 0) p.lse[static_cast<size_t>(bh) * p.T + qi] = (mm == -INFINITY) ? INFINITY : lse2 * kLn2;
+    }
     if (pass) {
       if (issuer) {
         tc_fence_after();
         mma_k_mn<DH>(tmem_o, sP, sV + bufi * L::TILE, t != nj);  // first tile of pass 1 overwrites
         umma_commit<1>(bar_o);
       }
-      if (waits) mbar_wait(bar_o, ph_o);  // P, K and V of this tile are free again; O is up to date
+      if (waits) mbar_wait_poll(bar_o, ph_o);  // P, K and V of this tile are free again; O is up to date
       ph_o ^= 1;
       tc_fence_after();
     }
   }
 
-  if (warp < 4) {  // O row -> bf16 -> [batch * T, heads * DH]
-    const uint32_t taddr = tmem_o + (static_cast<uint32_t>(warp * 32) << 16);
+  if (warp < kIssuerWarp) {  // O row -> bf16 -> [batch * T, heads * DH]
+    const uint32_t taddr = tmem_o + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     __nv_bfloat16* dst = p.out0 + static_cast<size_t>(row0 + r) * (p.H * DH) + col0;
 #pragma unroll 1
-    for (int c = 0; c < DH / 32; ++c) {
+    for (int c = half; c < DH / 32; c += 2) {
       float v[32];
       tmem_ld32(taddr + c * 32, v);
       tmem_ld_wait();
@@ -329,7 +346,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == kIssuerWarp) {
     tc_fence_after();
     tmem_dealloc<1>(tmem_s, 256);
   }
@@ -376,9 +393,9 @@ struct BwdSmem {
 template <bool kWriteP, bool kKMajor>
 __device__ __forceinline__ void tile_p_ds(uint32_t taddr_s, uint32_t taddr_dp, int r, int qi, int key0, const AttnParams& p,
                                           const uint8_t* mrow, float sl2, float lse2, float dl, uint8_t* sP, uint8_t* sDS,
-                                          bool all_visible) {
+                                          bool all_visible, int half) {
 #pragma unroll 1
-  for (int c = 0; c < 4; ++c) {
+  for (int c = 2 * half; c < 2 * half + 2; ++c) {
     float v[32], g[32];
     tmem_ld32(taddr_s + c * 32, v);
     tmem_ld32(taddr_dp + c * 32, g);
@@ -428,10 +445,10 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kb = blockIdx.x, bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
   const int col0 = h * DH, n_blk = p.T / QB;
-  const bool issuer = (warp == 4 && lane == 0);
+  const bool issuer = (warp == kIssuerWarp && lane == 0);
   // Lanes 1-31 of the issuing warp take no part in mbarrier waits: spinning beside the one lane that has to issue
   // the work the barrier is waiting for starves it.  They only join the __syncthreads.
-  const bool waits = (warp < 4 || lane == 0);
+  const bool waits = (warp < kIssuerWarp || lane == 0);
   if (issuer) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmK);
@@ -443,7 +460,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     mbar_init(bar_o, 1);
     fence_mbar_init();
   }
-  if (warp == 4) {
+  if (warp == kIssuerWarp) {
     tmem_alloc<1>(tmem_slot, 512);
     tmem_relinquish<1>();
   }
@@ -459,7 +476,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     load_tile<DH>(sK, &tmK, bar_kv, b * p.T + kb * QB, col0);
     load_tile<DH>(sV, &tmV, bar_kv, b * p.T + kb * QB, col0);
   }
-  const int r = threadIdx.x;
+  const int r = threadIdx.x & 127, half = threadIdx.x >> 7;
   const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
   const float sl2 = p.scale * kLog2e;
   uint32_t ph = 0;
@@ -476,16 +493,16 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       mma_kk<DH>(tmem_dp, sDO, sV, 128, false);   // dP = dO_i . V^T
       umma_commit<1>(bar_s);
     }
-    if (waits) mbar_wait(bar_s, ph);
+    if (waits) mbar_wait_poll(bar_s, ph);
     tc_fence_after();
-    if (warp < 4) {
+    if (warp < kIssuerWarp) {
       const int qi = i * QB + r;
       const size_t sidx = static_cast<size_t>(bh) * p.T + qi;
       const float lse = p.lse[sidx];
       const float lse2 = lse * kLog2e;  // +inf for a row that saw no key: every p is 0
-      const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
+      const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
       tile_p_ds<true, false>(tmem_s + lane_off, tmem_dp + lane_off, r, qi, kb * QB, p, mrow, sl2, lse2, p.delta[sidx], sP,
-                             sDS, tile_all_visible(i, kb, p.window, mrow));
+                             sDS, tile_all_visible(i, kb, p.window, mrow), half);
     }
     tc_fence_before();
     __syncthreads();
@@ -495,20 +512,20 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       mma_mn_mn<DH>(tmem_dk, sDS, sQ, i != i_lo);  // dK += dS^T . Q_i
       umma_commit<1>(bar_o);
     }
-    if (waits) mbar_wait(bar_o, ph);
+    if (waits) mbar_wait_poll(bar_o, ph);
     tc_fence_after();
     ph ^= 1;
   }
 
-  if (warp < 4) {  // accumulator lane = key row
-    const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
+  if (warp < kIssuerWarp) {  // accumulator lane = key row
+    const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
     const size_t row = static_cast<size_t>(b) * p.T + kb * QB + r;
 #pragma unroll 1
     for (int which = 0; which < 2; ++which) {
       __nv_bfloat16* dst = (which == 0 ? p.out0 : p.out1) + row * (p.H * DH) + col0;
       const uint32_t taddr = (which == 0 ? tmem_dk : tmem_dv) + lane_off;
 #pragma unroll 1
-      for (int c = 0; c < DH / 32; ++c) {
+      for (int c = half; c < DH / 32; c += 2) {
         float v[32];
         tmem_ld32(taddr + c * 32, v);
         tmem_ld_wait();
@@ -522,7 +539,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == kIssuerWarp) {
     tc_fence_after();
     tmem_dealloc<1>(tmem_s, 512);
   }
@@ -551,10 +568,10 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qb = blockIdx.x, bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
   const int col0 = h * DH;
-  const bool issuer = (warp == 4 && lane == 0);
+  const bool issuer = (warp == kIssuerWarp && lane == 0);
   // Lanes 1-31 of the issuing warp take no part in mbarrier waits: spinning beside the one lane that has to issue
   // the work the barrier is waiting for starves it.  They only join the __syncthreads.
-  const bool waits = (warp < 4 || lane == 0);
+  const bool waits = (warp < kIssuerWarp || lane == 0);
   if (issuer) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmK);
@@ -566,7 +583,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     mbar_init(bar_o, 1);
     fence_mbar_init();
   }
-  if (warp == 4) {
+  if (warp == kIssuerWarp) {
     tmem_alloc<1>(tmem_slot, 512);
     tmem_relinquish<1>();
   }
@@ -582,11 +599,11 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     load_tile<DH>(sQ, &tmQ, bar_q, b * p.T + qb * QB, col0);
     load_tile<DH>(sDO, &tmDO, bar_q, b * p.T + qb * QB, col0);
   }
-  const int r = threadIdx.x, qi = qb * QB + r;
+  const int r = threadIdx.x & 127, half = threadIdx.x >> 7, qi = qb * QB + r;
   const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
   const float sl2 = p.scale * kLog2e;
   float lse2 = 0.f, dl = 0.f;
-  if (warp < 4) {
+  if (warp < kIssuerWarp) {
     const size_t sidx = static_cast<size_t>(bh) * p.T + qi;
     lse2 = p.lse[sidx] * kLog2e;
     dl = p.delta[sidx];
@@ -605,12 +622,12 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       mma_kk<DH>(tmem_dp, sDO, sV, 128, false);  // dP = dO . V_j^T
       umma_commit<1>(bar_s);
     }
-    if (waits) mbar_wait(bar_s, ph);
+    if (waits) mbar_wait_poll(bar_s, ph);
     tc_fence_after();
-    if (warp < 4) {
-      const uint32_t lane_off = static_cast<uint32_t>(warp * 32) << 16;
+    if (warp < kIssuerWarp) {
+      const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
       tile_p_ds<false, true>(tmem_s + lane_off, tmem_dp + lane_off, r, qi, j * QB, p, mrow, sl2, lse2, dl, nullptr, sDS,
-                             tile_all_visible(qb, j, p.window, mrow));
+                             tile_all_visible(qb, j, p.window, mrow), half);
     }
     tc_fence_before();
     __syncthreads();
@@ -619,16 +636,16 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       mma_k_mn<DH>(tmem_dq, sDS, sK, j != j_lo);  // dQ += dS . K_j
       umma_commit<1>(bar_o);
     }
-    if (waits) mbar_wait(bar_o, ph);
+    if (waits) mbar_wait_poll(bar_o, ph);
     tc_fence_after();
     ph ^= 1;
   }
 
-  if (warp < 4) {
-    const uint32_t taddr = tmem_dq + (static_cast<uint32_t>(warp * 32) << 16);
+  if (warp < kIssuerWarp) {
+    const uint32_t taddr = tmem_dq + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     __nv_bfloat16* dst = p.out0 + (static_cast<size_t>(b) * p.T + qi) * (p.H * DH) + col0;
 #pragma unroll 1
-    for (int c = 0; c < DH / 32; ++c) {
+    for (int c = half; c < DH / 32; c += 2) {
       float v[32];
       tmem_ld32(taddr + c * 32, v);
       tmem_ld_wait();
@@ -641,7 +658,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 4) {
+  if (warp == kIssuerWarp) {
     tc_fence_after();
     tmem_dealloc<1>(tmem_s, 512);
   }
