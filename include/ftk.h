@@ -96,6 +96,8 @@ int ftk_set_option(int32_t key, int32_t value);
 #define FTK_TL_LINEAR_DX 14
 #define FTK_TL_ATTN_FWD 15
 #define FTK_TL_ATTN_BWD 16
+#define FTK_TL_LAYERNORM_FWD 17
+#define FTK_TL_LAYERNORM_BWD 18
 int ftk_timeline_enable(int32_t on);
 int ftk_timeline_read(int32_t* tags, float* ms, float* start_ms, int32_t max_n);
 
@@ -267,21 +269,48 @@ int ftk_scale_unless_one(void* buf, size_t n, int32_t dtype, const float* factor
  * TMA -> tcgen05.mma -> TMEM kernel template with a bias / GELU epilogue. Replaces torch.nn.Linear inside HF's
  * GPT-Neo / GPT-J blocks (the modules finetuner.py trains through model(**inputs), FT.py:479, with gradient
  * checkpointing on, FT.py:884) and the elementwise passes around their MLP activation.
- *   ftk_linear_fwd   Y[M,N] = act(X[M,K] . W[N,K]^T + bias[N]), all bf16; act FTK_ACT_GELU_NEW also stores the
- *                    pre-activation in `pre` (may be NULL) for the backward
+ *   ftk_linear_fwd   Y[M,N] = act(X[M,K] . W[N,K]^T + bias[N]) + residual[M,N], all bf16; bias and residual may be
+ *                    NULL; act FTK_ACT_GELU_NEW also stores the pre-activation in `pre` (may be NULL) for the
+ *                    backward. The residual (HF GPTNeoBlock.forward's `attn_output + residual` and
+ *                    `residual + feed_forward_hidden_states`) is added in fp32 before the one rounding to bf16 and
+ *                    may alias Y.
  *   ftk_linear_bwd   dX[M,K] = dY[M,N] . W            (NULL to skip), multiplied elementwise by gelu_new'(dx_mul_pre)
  *                    when dx_mul_pre (bf16 [M,K], the pre-activation of the GELU layer that produced X) is given:
- *                    the gradient leaves the GEMM already taken through the activation;
+ *                    the gradient leaves the GEMM already taken through the activation; plus dx_add[M,K] when given
+ *                    (may alias dX): layers that share an input (q_proj, k_proj, v_proj) chain their dX GEMMs
+ *                    instead of leaving two elementwise sums to autograd;
  *                    dW[N,K] (+)= dY^T . X           (NULL to skip; FTK_BF16 / FTK_F32, accumulate as elsewhere);
  *                    dbias[N] (+)= column sums of dY  (fp32, NULL to skip)
  * K and N must be multiples of 64.
  */
 #define FTK_ACT_NONE 0
 #define FTK_ACT_GELU_NEW 1
-int ftk_linear_fwd(const void* X, const void* W, const void* bias, int64_t M, int32_t K, int32_t N, int32_t act, void* Y,
-                   void* pre, void* stream);
-int ftk_linear_bwd(const void* X, const void* W, const void* dY, const void* dx_mul_pre, int64_t M, int32_t K, int32_t N,
-                   void* dX, void* dW, int32_t dw_dtype, int32_t accumulate, float* dbias, void* stream);
+int ftk_linear_fwd(const void* X, const void* W, const void* bias, const void* residual, int64_t M, int32_t K, int32_t N,
+                   int32_t act, void* Y, void* pre, void* stream);
+int ftk_linear_bwd(const void* X, const void* W, const void* dY, const void* dx_mul_pre, const void* dx_add, int64_t M,
+                   int32_t K, int32_t N, void* dX, void* dW, int32_t dw_dtype, int32_t accumulate, float* dbias,
+                   void* stream);
+
+/*
+ * LayerNorm of the transformer trunk. Replaces torch.nn.LayerNorm in HF's GPT-Neo blocks
+ * (GPTNeoBlock.ln_1 / ln_2 and GPTNeoModel.ln_f, reached from FT.py:479 model(**inputs) and re-run by gradient
+ * checkpointing, FT.py:884), its autograd, and the elementwise add that joins the residual branch's gradient to the
+ * LayerNorm's where the two fork. Arithmetic of torch.nn.functional.layer_norm on bf16 tensors: fp32 statistics
+ * (biased variance), rstd = 1 / sqrt(var + eps), one rounding at the end.
+ *   X, Y, dY, dX, dx_add   bf16 [M, D];   gamma, beta   bf16 [D] (beta may be NULL);   mean, rstd   fp32 [M]
+ *   ftk_layernorm_fwd   Y = (X - mean) * rstd * gamma + beta; also writes mean and rstd for the backward
+ *   ftk_layernorm_bwd   dX = the LayerNorm's input gradient (+ dx_add when given: the gradient that reached X along
+ *                       the residual branch; may alias dX); dgamma, dbeta fp32 [D] (dbeta may be NULL), summed over
+ *                       rows in a fixed order (deterministic, no atomics); workspace from
+ *                       ftk_layernorm_bwd_workspace (per-block partial column sums)
+ * Requirements: D a multiple of 256, at most 8192; 16-byte aligned buffers.
+ */
+int ftk_layernorm_fwd(const void* X, const void* gamma, const void* beta, int64_t M, int32_t D, float eps, void* Y,
+                      float* mean, float* rstd, void* stream);
+size_t ftk_layernorm_bwd_workspace(int64_t M, int32_t D);
+int ftk_layernorm_bwd(const void* dY, const void* X, const void* gamma, const float* mean, const float* rstd,
+                      const void* dx_add, int64_t M, int32_t D, void* dX, float* dgamma, float* dbeta, void* workspace,
+                      size_t workspace_bytes, void* stream);
 
 /*
  * Causal / local-window self-attention of the transformer trunk. Replaces HF GPT-Neo's eager

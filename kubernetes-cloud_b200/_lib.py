@@ -48,10 +48,15 @@ SIGNATURES = {
     "ftk_set_option": (c_int32, [c_int32, c_int32]),
     "ftk_timeline_enable": (c_int32, [c_int32]),
     "ftk_timeline_read": (c_int32, [c_void_p, c_void_p, c_void_p, c_int32]),
-    "ftk_linear_fwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_int32, c_void_p, c_void_p,
-                                 c_void_p]),
-    "ftk_linear_bwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p, c_void_p,
-                                 c_int32, c_int32, c_void_p, c_void_p]),
+    "ftk_linear_fwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_int32, c_void_p,
+                                 c_void_p, c_void_p]),
+    "ftk_linear_bwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_int32, c_void_p,
+                                 c_void_p, c_int32, c_int32, c_void_p, c_void_p]),
+    "ftk_layernorm_fwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_float, c_void_p, c_void_p, c_void_p,
+                                    c_void_p]),
+    "ftk_layernorm_bwd_workspace": (c_size_t, [c_int64, c_int32]),
+    "ftk_layernorm_bwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_int32, c_void_p,
+                                    c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "ftk_attention_fwd": (c_int32, [c_void_p, c_void_p, c_void_p, c_void_p, c_int32, c_int32, c_int32, c_int32, c_int32,
                                     c_float, c_void_p, c_void_p, c_void_p]),
     "ftk_attention_bwd_workspace": (c_size_t, [c_int32, c_int32, c_int32]),
@@ -126,7 +131,8 @@ def set_option(name: str, value: int) -> None:
 
 TIMELINE_TAGS = {1: "gather", 2: "fwd", 3: "fwd_keep", 4: "finalize", 5: "dz", 6: "convert", 7: "dH", 8: "dW",
                  9: "dbias", 10: "adamw", 11: "sqnorm", 12: "allreduce",
-                 13: "linear_fwd", 14: "linear_dx", 15: "attn_fwd", 16: "attn_bwd"}  # FTK_TL_* in include/ftk.h
+                 13: "linear_fwd", 14: "linear_dx", 15: "attn_fwd", 16: "attn_bwd", 17: "layernorm_fwd",
+                 18: "layernorm_bwd"}  # FTK_TL_* in include/ftk.h
 
 
 def timeline_enable(on: bool) -> None:

@@ -38,6 +38,7 @@ constexpr int kAttnThreads = 288;
 constexpr int kIssuerWarp = 8;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
+constexpr int kMaxKeyBlocks = 256;  // per-key-block padding flags kept in shared memory: T <= 32768 with a key mask
 
 struct AttnParams {
   const uint8_t* key_mask;  // [batch * T] (1 = may be attended) or null
@@ -171,14 +172,53 @@ __device__ __forceinline__ void mask_scores(float* v, int qi, int key0, const At
 }
 
 // ------------------------------------------------------------------------------------------------ forward
+// Which 128-key blocks of one sequence hold no padding (every mask byte non-zero)?  With those known, a tile only pays
+// for the per-element padding test where padding really is; HF always hands the layers an attention mask, and in a
+// training batch it is all ones except in the last context of the token file.  Called by the 256 row threads.
+__device__ __forceinline__ void key_block_flags(const uint8_t* mrow, int T, uint8_t* blk_ok, int tid, int lane) {
+  for (int base = 0; base < T; base += 256 * 16) {
+    const int off = base + tid * 16;
+    bool ok = true;
+    if (off < T) {
+      const uint4 mk = *reinterpret_cast<const uint4*>(mrow + off);
+      const uint32_t w[4] = {mk.x, mk.y, mk.z, mk.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) ok = ok && (((w[e] - 0x01010101u) & ~w[e] & 0x80808080u) == 0u);  // no zero byte
+    }
+    const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+    if ((lane & 7) == 0 && off < T) blk_ok[off >> 7] = (((bal >> lane) & 0xffu) == 0xffu) ? 1 : 0;
+  }
+}
+
+// 32 raw scores of one query row -> -inf where the key must not be attended (the forward scales afterwards).
+__device__ __forceinline__ void mask_raw(float* v, int qi, int key0, int window, const uint8_t* mrow) {
+  uint32_t mbits = 0xffffffffu;
+  if (mrow != nullptr) {
+    const uint4 m0 = *reinterpret_cast<const uint4*>(mrow + key0), m1 = *reinterpret_cast<const uint4*>(mrow + key0 + 16);
+    const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
+    mbits = 0;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) mbits |= ((mw[j >> 2] >> ((j & 3) * 8)) & 0xffu) ? (1u << j) : 0u;
+  }
+#pragma unroll
+  for (int j = 0; j < 32; ++j)
+    if (!(visible(qi, key0 + j, window) && ((mbits >> j) & 1u))) v[j] = -INFINITY;
+}
+
 template <int DH>
 struct FwdSmem {
   static constexpr uint32_t TILE = QB * DH * 2;  // one [128 x DH] bf16 operand tile
   static constexpr uint32_t Q_OFF = 0, K_OFF = TILE, V_OFF = 3 * TILE, P_OFF = 5 * TILE, BAR_OFF = P_OFF + 32768;
-  static constexpr uint32_t STAT_OFF = BAR_OFF + 128;  // [2][256] floats: the two column halves' softmax statistics
-  static constexpr uint32_t BYTES = 1024 + STAT_OFF + 2048;
+  static constexpr uint32_t STAT_OFF = BAR_OFF + 128;    // [256] floats: the two column halves' row statistics
+  static constexpr uint32_t FLAG_OFF = STAT_OFF + 1024;  // [kMaxKeyBlocks] bytes: key block holds no padding
+  static constexpr uint32_t BYTES = 1024 + FLAG_OFF + kMaxKeyBlocks;
 };
 
+// Schedule.  Tiles t = 0 .. 2 nj - 1: pass 0 (row maxima only: no exponentials) over the nj key blocks the query block
+// sees, then pass 1 (P = exp2(s - max) as bf16, row sums in fp32, O += P.V; O / sum at the end).  The scores have two
+// TMEM buffers: while the row threads work on S(t) the tensor pipe already forms S(t+1), and P.V of tile t runs while
+// they work on tile t+1 (they wait for it only at the point where they overwrite the P tile).  K and V each have two
+// shared-memory buffers with their own barriers; a buffer is refilled as soon as the MMA that read it has completed.
 template <int DH>
 __global__ void __launch_bounds__(kAttnThreads, 1)
     attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
@@ -190,147 +230,156 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   uint8_t* sK = smem + L::K_OFF;  // two buffers
   uint8_t* sV = smem + L::V_OFF;  // two buffers
   uint8_t* sP = smem + L::P_OFF;
-  uint64_t* bar_kv = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);  // [2]
-  uint64_t* bar_q = bar_kv + 2;
-  uint64_t* bar_s = bar_kv + 3;
-  uint64_t* bar_o = bar_kv + 4;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_kv + 5);
-  float* stat_m = reinterpret_cast<float*>(smem + L::STAT_OFF);
-  float* stat_l = stat_m + 256;
+  uint64_t* bar_q = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
+  uint64_t* bar_k = bar_q + 1;  // [2]
+  uint64_t* bar_v = bar_q + 3;  // [2]
+  uint64_t* bar_s = bar_q + 5;  // [2]
+  uint64_t* bar_o = bar_q + 7;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_q + 8);
+  float* stat = reinterpret_cast<float*>(smem + L::STAT_OFF);
+  uint8_t* blk_ok = smem + L::FLAG_OFF;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int qb = blockIdx.x, bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
+  // the query blocks that see the most keys start first, so the short ones fill the tail of the grid
+  const int qb = static_cast<int>(gridDim.x) - 1 - static_cast<int>(blockIdx.x);
+  const int bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
   const int row0 = b * p.T + qb * QB;  // first row of this block in the [batch * T] matrices
   const int col0 = h * DH;
   const bool issuer = (warp == kIssuerWarp && lane == 0);
-  // Lanes 1-31 of the issuing warp take no part in mbarrier waits: spinning beside the one lane that has to issue
-  // the work the barrier is waiting for starves it.  They only join the __syncthreads.
-  const bool waits = (warp < kIssuerWarp || lane == 0);
+  const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
 
   if (issuer) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmK);
     tma_prefetch_desc(&tmV);
-    mbar_init(&bar_kv[0], 1);
-    mbar_init(&bar_kv[1], 1);
-    mbar_init(bar_q, 1);
-    mbar_init(bar_s, 1);
-    mbar_init(bar_o, 1);
+    for (int i = 0; i < 8; ++i) mbar_init(bar_q + i, 1);
     fence_mbar_init();
   }
   if (warp == kIssuerWarp) {
-    tmem_alloc<1>(tmem_slot, 256);
+    tmem_alloc<1>(tmem_slot, 512);
     tmem_relinquish<1>();
+  } else if (mrow != nullptr) {
+    key_block_flags(mrow, p.T, blk_ok, threadIdx.x, lane);
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_s = *tmem_slot, tmem_o = tmem_s + 128;
+  const uint32_t tmem_s = *tmem_slot, tmem_o = tmem_s + 256;  // S buffers at +0 and +128
 
   int j_lo, j_hi;
   kv_range(qb, p.window, j_lo, j_hi);
-  const int nj = j_hi - j_lo + 1, n_tiles = 2 * nj;  // pass 0 over the key blocks, then pass 1
-  auto issue_load = [&](int t) {  // operands of tile t into buffer t & 1 (K only in pass 0)
-    const int pass = t >= nj, j = j_lo + (pass ? t - nj : t), bufi = t & 1;
-    mbar_arrive_expect_tx(&bar_kv[bufi], pass ? 2 * L::TILE : L::TILE);
-    load_tile<DH>(sK + bufi * L::TILE, &tmK, &bar_kv[bufi], b * p.T + j * QB, col0);
-    if (pass) load_tile<DH>(sV + bufi * L::TILE, &tmV, &bar_kv[bufi], b * p.T + j * QB, col0);
+  const int nj = j_hi - j_lo + 1, n_tiles = 2 * nj;
+  auto load_k = [&](int t) {  // K block of tile t -> K buffer t & 1
+    const int bi = t & 1, u = t >= nj ? t - nj : t;
+    mbar_arrive_expect_tx(&bar_k[bi], L::TILE);
+    load_tile<DH>(sK + bi * L::TILE, &tmK, &bar_k[bi], b * p.T + (j_lo + u) * QB, col0);
+  };
+  auto load_v = [&](int u) {  // V block of pass-1 tile u -> V buffer u & 1
+    const int bi = u & 1;
+    mbar_arrive_expect_tx(&bar_v[bi], L::TILE);
+    load_tile<DH>(sV + bi * L::TILE, &tmV, &bar_v[bi], b * p.T + (j_lo + u) * QB, col0);
+  };
+  auto issue_s = [&](int t) {  // S(t) = Q.K(t)^T into S buffer t & 1
+    const int bi = t & 1;
+    mbar_wait(&bar_k[bi], (t >> 1) & 1);
+    tc_fence_after();
+    mma_kk<DH>(tmem_s + bi * 128, sQ, sK + bi * L::TILE, 128, false);
+    umma_commit<1>(&bar_s[bi]);
   };
   if (issuer) {
     mbar_arrive_expect_tx(bar_q, L::TILE);
     load_tile<DH>(sQ, &tmQ, bar_q, row0, col0);
-    issue_load(0);
+    load_k(0);
+    load_k(1);  // n_tiles >= 2
+    load_v(0);
+    if (nj > 1) load_v(1);
+    mbar_wait(bar_q, 0);
+    issue_s(0);
   }
 
-  const int r = threadIdx.x & 127, half = threadIdx.x >> 7;  // row threads: accumulator row and column half
-  const int qi = qb * QB + r;           // position of this thread's query inside its sequence
-  const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
-  const float sl2 = p.scale * kLog2e;
-  float m = -INFINITY, l = 0.f, lse2 = 0.f;  // running max / sum in the exp2 domain; lse2 = log2-sum-exp
-  uint32_t ph_s = 0, ph_o = 0;
-  if (waits) mbar_wait(bar_q, 0);
+  const int r = threadIdx.x & 127, half = (threadIdx.x >> 7) & 1;  // row threads: accumulator row and column half
+  const int qi = qb * QB + r;                                      // position of this thread's query in its sequence
+  const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
+  const float sl2 = p.scale * kLog2e;  // scale > 0 (checked on the host): max(scale * s) = scale * max(s)
+  float m_raw = -INFINITY;             // pass 0: running maximum of this thread's half of the row, unscaled
+  float m2 = 0.f, l = 0.f;             // pass 1: the row's maximum in the exp2 domain (0 if it sees no key), partial sum
+  bool row_empty = false;
 
   for (int t = 0; t < n_tiles; ++t) {
-    const int pass = t >= nj, j = j_lo + (pass ? t - nj : t), bufi = t & 1;
+    const int pass = t >= nj, u = pass ? t - nj : t, j = j_lo + u, bi = t & 1;
+    const uint32_t par = (t >> 1) & 1;
     if (issuer) {
-      if (t + 1 < n_tiles) issue_load(t + 1);  // its buffer was last used by tile t - 1, whose MMAs have completed
-      mbar_wait(&bar_kv[bufi], (t >> 1) & 1);
+      mbar_wait(&bar_s[bi], par);           // S(t) is complete: its K buffer is free
+      if (t + 2 < n_tiles) load_k(t + 2);
+      if (t + 1 < n_tiles) issue_s(t + 1);  // S buffer (t+1) & 1 was last read for tile t-1, before that tile's sync
+    } else if (warp < kIssuerWarp) {
+      mbar_wait_poll(&bar_s[bi], par);
       tc_fence_after();
-      mma_kk<DH>(tmem_s, sQ, sK + bufi * L::TILE, 128, false);
-      umma_commit<1>(bar_s);
-    }
-    if (waits) mbar_wait_poll(bar_s, ph_s);
-    ph_s ^= 1;
-    tc_fence_after();
-    if (warp < kIssuerWarp) {
-      const uint32_t taddr = tmem_s + (static_cast<uint32_t>((warp & 3) * 32) << 16);
-      if (pass == 0) {
-#pragma unroll 1
-        for (int c = 2 * half; c < 2 * half + 2; ++c) {
-          float v[32];
-          tmem_ld32(taddr + c * 32, v);
-          tmem_ld_wait();
-          mask_scores(v, qi, j * QB + c * 32, p, mrow, sl2, tile_all_visible(qb, j, p.window, mrow));
-          float cm = v[0];
+      const uint8_t* mr = (mrow != nullptr && !blk_ok[j]) ? mrow : nullptr;
+      const bool all_vis = tile_all_visible(qb, j, p.window, mr);
+      const int key0 = j * QB + half * 64;
+      float v[64];
+      tmem_ld64(tmem_s + bi * 128 + lane_off + half * 64, v);
+      tmem_ld_wait();
+      if (!all_vis) {
+        mask_raw(v, qi, key0, p.window, mr);
+        mask_raw(v + 32, qi, key0 + 32, p.window, mr);
+      }
+      if (!pass) {
+        float c0 = fmaxf(v[0], v[1]), c1 = fmaxf(v[2], v[3]);
 #pragma unroll
-          for (int e = 1; e < 32; ++e) cm = fmaxf(cm, v[e]);
-          const float mn = fmaxf(m, cm);
-          if (mn != -INFINITY) {
-            float acc = 0.f;
-#pragma unroll
-            for (int e = 0; e < 32; ++e) acc += fast_exp2(v[e] - mn);
-            l = l * fast_exp2(m - mn) + acc;  // exp2(-inf) = 0 while nothing has been seen
-            m = mn;
-          }
+        for (int e = 4; e < 64; e += 4) {
+          c0 = fmaxf(c0, fmaxf(v[e], v[e + 1]));
+          c1 = fmaxf(c1, fmaxf(v[e + 2], v[e + 3]));
         }
-        if (t == nj - 1) {  // end of pass 0: publish this column half's statistics of the row
-          stat_m[threadIdx.x] = m;
-          stat_l[threadIdx.x] = l;
-        }
+        m_raw = fmaxf(m_raw, fmaxf(c0, c1));
+        if (t == nj - 1) stat[threadIdx.x] = m_raw;
       } else {
-#pragma unroll 1
-        for (int c = 2 * half; c < 2 * half + 2; ++c) {
-          float v[32];
-          tmem_ld32(taddr + c * 32, v);
-          tmem_ld_wait();
-          mask_scores(v, qi, j * QB + c * 32, p, mrow, sl2, tile_all_visible(qb, j, p.window, mrow));
+        uint32_t w[32];
+        float l0 = 0.f, l1 = 0.f;
 #pragma unroll
-          for (int q8 = 0; q8 < 4; ++q8) {
-            uint32_t w[4];
-#pragma unroll
-            for (int e = 0; e < 4; ++e)
-              w[e] = pack2(fast_exp2(v[q8 * 8 + 2 * e] - lse2), fast_exp2(v[q8 * 8 + 2 * e + 1] - lse2));
-            put8_kmajor(sP, r, c * 32 + q8 * 8, w);
-          }
+        for (int e = 0; e < 32; ++e) {
+          const float p0 = fast_exp2(fmaf(v[2 * e], sl2, -m2)), p1 = fast_exp2(fmaf(v[2 * e + 1], sl2, -m2));
+          l0 += p0;
+          l1 += p1;
+          w[e] = pack2(p0, p1);
         }
-        fence_async_shared();  // the P tile was written through the generic proxy; the MMA reads it through the async one
+        l += l0 + l1;
+        if (u > 0) mbar_wait_poll(bar_o, (u - 1) & 1);  // P.V of the previous tile has read the P tile
+#pragma unroll
+        for (int q8 = 0; q8 < 8; ++q8) put8_kmajor(sP, r, half * 64 + q8 * 8, &w[q8 * 4]);
+        fence_async_shared();  // P was written through the generic proxy; the MMA reads it through the async one
       }
     }
     tc_fence_before();
     __syncthreads();
-    if (t == nj - 1 && warp < kIssuerWarp) {  // merge the two halves: log2-sum-exp of the whole row
-      const float m0 = stat_m[r], m1 = stat_m[r + 128], mm = fmaxf(m0, m1);
-      if (mm == -INFINITY) {
-        lse2 = INFINITY;  // a row that sees no key: every p becomes 0
-      } else {
-        lse2 = mm + log2f(stat_l[r] * fast_exp2(m0 - mm) + stat_l[r + 128] * fast_exp2(m1 - mm));
-      }
-      if (half == 0) p.lse[static_cast<size_t>(bh) * p.T + qi] = (mm == -INFINITY) ? INFINITY : lse2 * kLn2;
+    if (t == nj - 1 && warp < kIssuerWarp) {  // end of pass 0: the row's maximum from its two halves
+      const float mm = fmaxf(stat[r], stat[r + 128]);
+      row_empty = (mm == -INFINITY);  // a row that sees no key: every p becomes exp2(-inf - 0) = 0
+      m2 = row_empty ? 0.f : mm * sl2;
     }
-    if (pass) {
-      if (issuer) {
-        tc_fence_after();
-        mma_k_mn<DH>(tmem_o, sP, sV + bufi * L::TILE, t != nj);  // first tile of pass 1 overwrites
-        umma_commit<1>(bar_o);
-      }
-      if (waits) mbar_wait_poll(bar_o, ph_o);  // P, K and V of this tile are free again; O is up to date
-      ph_o ^= 1;
+    if (pass && issuer) {
+      if (u > 0) mbar_wait(bar_o, (u - 1) & 1);  // (already complete: the row threads waited for it) V buffer (u+1) & 1 is free
+      if (u >= 1 && u + 1 < nj) load_v(u + 1);
+      mbar_wait(&bar_v[u & 1], (u >> 1) & 1);
       tc_fence_after();
+      mma_k_mn<DH>(tmem_o, sP, sV + (u & 1) * L::TILE, u != 0);  // first tile of pass 1 overwrites
+      umma_commit<1>(bar_o);
     }
   }
 
-  if (warp < kIssuerWarp) {  // O row -> bf16 -> [batch * T, heads * DH]
-    const uint32_t taddr = tmem_o + (static_cast<uint32_t>((warp & 3) * 32) << 16);
+  if (warp < kIssuerWarp) {
+    stat[threadIdx.x] = l;  // (the maxima were read a whole pass ago)
+    mbar_wait_poll(bar_o, (nj - 1) & 1);  // the last P.V: O is complete
+    tc_fence_after();
+  }
+  __syncthreads();
+  if (warp < kIssuerWarp) {  // O row / sum -> bf16 -> [batch * T, heads * DH]
+    const float lsum = stat[r] + stat[r + 128];
+    const float inv = lsum > 0.f ? 1.f / lsum : 0.f;
+    if (half == 0)
+      p.lse[static_cast<size_t>(bh) * p.T + qi] = (row_empty || !(lsum > 0.f)) ? INFINITY : (m2 + log2f(lsum)) * kLn2;
+    const uint32_t taddr = tmem_o + lane_off;
     __nv_bfloat16* dst = p.out0 + static_cast<size_t>(row0 + r) * (p.H * DH) + col0;
 #pragma unroll 1
     for (int c = half; c < DH / 32; c += 2) {
@@ -340,15 +389,15 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
 #pragma unroll
       for (int q8 = 0; q8 < 4; ++q8)
         *reinterpret_cast<uint4*>(dst + c * 32 + q8 * 8) =
-            make_uint4(pack2(v[q8 * 8], v[q8 * 8 + 1]), pack2(v[q8 * 8 + 2], v[q8 * 8 + 3]),
-                       pack2(v[q8 * 8 + 4], v[q8 * 8 + 5]), pack2(v[q8 * 8 + 6], v[q8 * 8 + 7]));
+            make_uint4(pack2(v[q8 * 8] * inv, v[q8 * 8 + 1] * inv), pack2(v[q8 * 8 + 2] * inv, v[q8 * 8 + 3] * inv),
+                       pack2(v[q8 * 8 + 4] * inv, v[q8 * 8 + 5] * inv), pack2(v[q8 * 8 + 6] * inv, v[q8 * 8 + 7] * inv));
     }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == kIssuerWarp) {
     tc_fence_after();
-    tmem_dealloc<1>(tmem_s, 256);
+    tmem_dealloc<1>(tmem_s, 512);
   }
 }
 
@@ -385,7 +434,8 @@ struct BwdSmem {
   // stationary pair, streamed pair, then the two [128 x 128] tiles the row threads write (P and dS)
   static constexpr uint32_t A_OFF = 0, B_OFF = TILE, C_OFF = 2 * TILE, D_OFF = 3 * TILE, P_OFF = 4 * TILE,
                             DS_OFF = P_OFF + 32768, BAR_OFF = DS_OFF + 32768;
-  static constexpr uint32_t BYTES = 1024 + BAR_OFF + 8 * 8 + 16;
+  static constexpr uint32_t FLAG_OFF = BAR_OFF + 8 * 8 + 16;  // [kMaxKeyBlocks] bytes: key block holds no padding
+  static constexpr uint32_t BYTES = 1024 + FLAG_OFF + kMaxKeyBlocks;
 };
 
 // One thread's 128 scores and 128 dP values of a tile -> P and dS (8 columns at a time, straight into shared memory).
@@ -460,14 +510,27 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     mbar_init(bar_o, 1);
     fence_mbar_init();
   }
+  const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
+  uint8_t* blk_ok = smem + L::FLAG_OFF;
   if (warp == kIssuerWarp) {
     tmem_alloc<1>(tmem_slot, 512);
     tmem_relinquish<1>();
+  } else if (mrow != nullptr && warp == 0) {  // does this key block hold any padding?  (8 lanes x 16 mask bytes)
+    bool ok = true;
+    if (lane < 8) {
+      const uint4 mk = *reinterpret_cast<const uint4*>(mrow + kb * QB + lane * 16);
+      const uint32_t w[4] = {mk.x, mk.y, mk.z, mk.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) ok = ok && (((w[e] - 0x01010101u) & ~w[e] & 0x80808080u) == 0u);
+    }
+    ok = __all_sync(0xffffffffu, ok);
+    if (lane == 0) blk_ok[0] = ok ? 1 : 0;
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_s = *tmem_slot, tmem_dp = tmem_s + 128, tmem_dv = tmem_s + 256, tmem_dk = tmem_s + 384;
+  if (mrow != nullptr && blk_ok[0]) mrow = nullptr;  // no padding among this block's keys: geometric tests only
 
   int i_lo, i_hi;
   q_range(kb, p.window, n_blk, i_lo, i_hi);
@@ -477,7 +540,6 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     load_tile<DH>(sV, &tmV, bar_kv, b * p.T + kb * QB, col0);
   }
   const int r = threadIdx.x & 127, half = threadIdx.x >> 7;
-  const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
   const float sl2 = p.scale * kLog2e;
   uint32_t ph = 0;
   if (waits) mbar_wait(bar_kv, 0);
@@ -566,7 +628,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_q + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int qb = blockIdx.x, bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
+  const int qb = static_cast<int>(gridDim.x) - 1 - static_cast<int>(blockIdx.x);  // longest key ranges first
+  const int bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
   const int col0 = h * DH;
   const bool issuer = (warp == kIssuerWarp && lane == 0);
   // Lanes 1-31 of the issuing warp take no part in mbarrier waits: spinning beside the one lane that has to issue
@@ -583,9 +646,13 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     mbar_init(bar_o, 1);
     fence_mbar_init();
   }
+  const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
+  uint8_t* blk_ok = smem + L::FLAG_OFF;
   if (warp == kIssuerWarp) {
     tmem_alloc<1>(tmem_slot, 512);
     tmem_relinquish<1>();
+  } else if (mrow != nullptr) {
+    key_block_flags(mrow, p.T, blk_ok, threadIdx.x, lane);
   }
   tc_fence_before();
   __syncthreads();
@@ -600,7 +667,6 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     load_tile<DH>(sDO, &tmDO, bar_q, b * p.T + qb * QB, col0);
   }
   const int r = threadIdx.x & 127, half = threadIdx.x >> 7, qi = qb * QB + r;
-  const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
   const float sl2 = p.scale * kLog2e;
   float lse2 = 0.f, dl = 0.f;
   if (warp < kIssuerWarp) {
@@ -626,8 +692,9 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     tc_fence_after();
     if (warp < kIssuerWarp) {
       const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
-      tile_p_ds<false, true>(tmem_s + lane_off, tmem_dp + lane_off, r, qi, j * QB, p, mrow, sl2, lse2, dl, nullptr, sDS,
-                             tile_all_visible(qb, j, p.window, mrow), half);
+      const uint8_t* mr = (mrow != nullptr && !blk_ok[j]) ? mrow : nullptr;
+      tile_p_ds<false, true>(tmem_s + lane_off, tmem_dp + lane_off, r, qi, j * QB, p, mr, sl2, lse2, dl, nullptr, sDS,
+                             tile_all_visible(qb, j, p.window, mr), half);
     }
     tc_fence_before();
     __syncthreads();
@@ -665,12 +732,15 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
 }
 
 // ------------------------------------------------------------------------------------------------ host side
-int check_attn(const void* q, const void* k, const void* v, int B, int T, int H, int DH, ftk::DeviceInfo* di) {
+int check_attn(const void* q, const void* k, const void* v, int B, int T, int H, int DH, float scale,
+               ftk::DeviceInfo* di) {
   FTK_REQUIRE(q && k && v, "ftk_attention: null Q, K or V");
   FTK_REQUIRE(B > 0 && H > 0 && T > 0 && T % QB == 0, "ftk_attention: T=%d must be a positive multiple of %d (B=%d, H=%d)", T,
               QB, B, H);
   FTK_REQUIRE(DH == 64 || DH == 128, "ftk_attention: head_dim %d is not 64 or 128", DH);
   FTK_REQUIRE(static_cast<int64_t>(B) * T < (int64_t(1) << 31), "ftk_attention: batch * T too large");
+  FTK_REQUIRE(T <= kMaxKeyBlocks * QB, "ftk_attention: T=%d exceeds %d", T, kMaxKeyBlocks * QB);
+  FTK_REQUIRE(scale > 0.f, "ftk_attention: scale must be positive, not %g", static_cast<double>(scale));
   if (int rc = ftk::get_device_info(di)) return rc;
   if (di->cc_major != 10)
     return ftk::fail(FTK_EUNSUPPORTED, "ftk_attention needs an sm_100 device (tcgen05/TMEM); found sm_%d%d", di->cc_major,
@@ -736,7 +806,7 @@ extern "C" int ftk_attention_fwd(const void* Q, const void* K, const void* V, co
                                  int32_t H, int32_t head_dim, int32_t window, float scale, void* O, float* lse,
                                  void* stream) {
   ftk::DeviceInfo di;
-  if (int rc = check_attn(Q, K, V, B, T, H, head_dim, &di)) return rc;
+  if (int rc = check_attn(Q, K, V, B, T, H, head_dim, scale, &di)) return rc;
   FTK_REQUIRE(O && lse, "ftk_attention_fwd: null output");
   FTK_REQUIRE(window >= 0, "ftk_attention_fwd: negative window");
   AttnParams p = {};
@@ -761,7 +831,7 @@ extern "C" int ftk_attention_bwd(const void* Q, const void* K, const void* V, co
                                  int32_t head_dim, int32_t window, float scale, void* dQ, void* dK, void* dV,
                                  void* workspace, size_t workspace_bytes, void* stream) {
   ftk::DeviceInfo di;
-  if (int rc = check_attn(Q, K, V, B, T, H, head_dim, &di)) return rc;
+  if (int rc = check_attn(Q, K, V, B, T, H, head_dim, scale, &di)) return rc;
   FTK_REQUIRE(O && dO && lse && dQ && dK && dV && workspace, "ftk_attention_bwd: null pointer argument");
   FTK_REQUIRE(window >= 0, "ftk_attention_bwd: negative window");
   if (workspace_bytes < ftk_attention_bwd_workspace(B, T, H))

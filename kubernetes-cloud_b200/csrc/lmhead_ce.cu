@@ -478,6 +478,8 @@ struct StoreEpi {
 //             the value the backward needs;
 //   mul_pre != null: out = acc * gelu_new'(mul_pre[row, col]) -- the dX GEMM of the layer AFTER a GELU hands back the
 //             gradient with respect to the pre-activation directly, so no elementwise pass ever touches [M, 4d].
+//   residual != null: out += residual[row, col] (last, in fp32 before the one rounding): the block's residual
+//             connection in the forward, the sum of several layers' input gradients in the backward.  May alias out.
 struct LinearEpi {
   static constexpr uint32_t kSmemBytes = 0;
   struct Params {
@@ -485,6 +487,7 @@ struct LinearEpi {
     __nv_bfloat16* pre;
     const __nv_bfloat16* bias;
     const __nv_bfloat16* mul_pre;
+    const __nv_bfloat16* residual;
     int rows, cols, ld, act;
   };
   struct State {
@@ -551,6 +554,16 @@ struct LinearEpi {
                                                                         pack_bf16x2(x[4], x[5]), pack_bf16x2(x[6], x[7]));
 #pragma unroll
             for (int e = 0; e < 8; ++e) x[e] = gelu_new(x[e]);
+          }
+          if (p.residual != nullptr) {
+            const uint4 rw = *(reinterpret_cast<const uint4*>(p.residual + off) + q);
+            const uint32_t r4[4] = {rw.x, rw.y, rw.z, rw.w};
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&r4[e]);
+              x[2 * e] += __low2float(h);
+              x[2 * e + 1] += __high2float(h);
+            }
           }
           *(reinterpret_cast<uint4*>(p.out + off) + q) = make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]),
                                                                     pack_bf16x2(x[4], x[5]), pack_bf16x2(x[6], x[7]));
@@ -1935,19 +1948,21 @@ int run_linear_gemm(const void* A, const void* B, int64_t M, int Kd, int N, cons
 
 }  // namespace
 
-extern "C" int ftk_linear_fwd(const void* X, const void* W, const void* bias, int64_t M, int32_t K, int32_t N,
-                              int32_t act, void* Y, void* pre, void* stream) {
+extern "C" int ftk_linear_fwd(const void* X, const void* W, const void* bias, const void* residual, int64_t M, int32_t K,
+                              int32_t N, int32_t act, void* Y, void* pre, void* stream) {
   ftk::DeviceInfo di;
   if (int rc = check_linear(X, W, M, K, N, &di)) return rc;
   FTK_REQUIRE(Y != nullptr, "ftk_linear_fwd: null output");
   FTK_REQUIRE(act == FTK_ACT_NONE || act == FTK_ACT_GELU_NEW, "ftk_linear_fwd: bad activation code %d", act);
-  FTK_REQUIRE(((reinterpret_cast<uintptr_t>(Y) | reinterpret_cast<uintptr_t>(pre) | reinterpret_cast<uintptr_t>(bias)) & 15) == 0,
-              "ftk_linear_fwd: Y / pre / bias must be 16-byte aligned");
+  FTK_REQUIRE(((reinterpret_cast<uintptr_t>(Y) | reinterpret_cast<uintptr_t>(pre) | reinterpret_cast<uintptr_t>(bias) |
+                reinterpret_cast<uintptr_t>(residual)) & 15) == 0,
+              "ftk_linear_fwd: Y / pre / bias / residual must be 16-byte aligned");
   LinearEpi::Params ep;
   ep.out = static_cast<__nv_bfloat16*>(Y);
   ep.pre = static_cast<__nv_bfloat16*>(pre);
   ep.bias = static_cast<const __nv_bfloat16*>(bias);
   ep.mul_pre = nullptr;
+  ep.residual = static_cast<const __nv_bfloat16*>(residual);
   ep.rows = static_cast<int>(M);
   ep.cols = N;
   ep.ld = N;
@@ -1958,15 +1973,16 @@ extern "C" int ftk_linear_fwd(const void* X, const void* W, const void* bias, in
   return run_linear_gemm<1, false>(X, W, M, K, N, ep, di.sm_count, st, FTK_TL_LINEAR_FWD);
 }
 
-extern "C" int ftk_linear_bwd(const void* X, const void* W, const void* dY, const void* dx_mul_pre, int64_t M,
-                              int32_t K, int32_t N, void* dX, void* dW, int32_t dw_dtype, int32_t accumulate,
+extern "C" int ftk_linear_bwd(const void* X, const void* W, const void* dY, const void* dx_mul_pre, const void* dx_add,
+                              int64_t M, int32_t K, int32_t N, void* dX, void* dW, int32_t dw_dtype, int32_t accumulate,
                               float* dbias, void* stream) {
   ftk::DeviceInfo di;
   if (int rc = check_linear(X, W, M, K, N, &di)) return rc;
   FTK_REQUIRE(dY != nullptr, "ftk_linear_bwd: null dY");
   FTK_REQUIRE(dw_dtype == FTK_BF16 || dw_dtype == FTK_F32, "ftk_linear_bwd: bad dw_dtype %d", dw_dtype);
-  FTK_REQUIRE(((reinterpret_cast<uintptr_t>(dX) | reinterpret_cast<uintptr_t>(dW) | reinterpret_cast<uintptr_t>(dx_mul_pre)) & 15) == 0,
-              "ftk_linear_bwd: dX / dW / dx_mul_pre must be 16-byte aligned");
+  FTK_REQUIRE(((reinterpret_cast<uintptr_t>(dX) | reinterpret_cast<uintptr_t>(dW) | reinterpret_cast<uintptr_t>(dx_mul_pre) |
+                reinterpret_cast<uintptr_t>(dx_add)) & 15) == 0,
+              "ftk_linear_bwd: dX / dW / dx_mul_pre / dx_add must be 16-byte aligned");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool pair = cta_group() == 2 && di.sm_count >= 2;
   if (dX != nullptr) {  // dX[M, K] = dY[M, N] . W[N, K]  (times gelu_new'(dx_mul_pre) when given)
@@ -1975,6 +1991,7 @@ extern "C" int ftk_linear_bwd(const void* X, const void* W, const void* dY, cons
     ep.pre = nullptr;
     ep.bias = nullptr;
     ep.mul_pre = static_cast<const __nv_bfloat16*>(dx_mul_pre);
+    ep.residual = static_cast<const __nv_bfloat16*>(dx_add);
     ep.rows = static_cast<int>(M);
     ep.cols = K;
     ep.ld = K;
