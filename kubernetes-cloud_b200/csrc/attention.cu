@@ -9,17 +9,21 @@
 // split / merge copies); one CTA owns a 128-row block of one (batch, head).
 //
 // Forward, two passes over the key blocks so that the output accumulator never needs rescaling:
-//   pass 0   S = Q.K^T (tcgen05.mma, accumulator in TMEM) -> masked row max / sum-exp -> lse
-//   pass 1   S again -> P = exp(S - lse) as bf16 into swizzled shared memory -> O += P.V (second tcgen05.mma)
-// Backward, two kernels, no atomics:
-//   kv-stationary   for a key block: over the query blocks that see it, S and dP = dO.V^T -> P, dS = P*(dP - D)
-//                   -> dV += P^T.dO, dK += dS^T.Q      (both accumulators stay in TMEM)
-//   q-stationary    for a query block: S, dP again -> dS -> dQ += dS.K
+//   pass 0   S = Q.K^T (tcgen05.mma, accumulator in TMEM) -> masked row maximum (no exponentials)
+//   pass 1   S again -> P = exp2(S - max) as bf16 into swizzled shared memory, row sums in fp32 -> O += P.V (second
+//            tcgen05.mma); O / sum and lse at the end
+// Backward, two kernels, no atomics, over 64-wide sub-tiles of the streamed operand:
+//   kv-stationary   for a key block, transposed (accumulator lanes = keys): over the query sub-blocks that see it,
+//                   S^T = K.Q_i^T and dP^T = V.dO_i^T -> P^T, dS^T = P^T * (dP^T - D) -> dV += P^T.dO_i, dK += dS^T.Q_i
+//   q-stationary    for a query block: S = Q.K_j^T, dP = dO.V_j^T again -> dS -> dQ += dS.K_j
 // The extra S / dP recomputations cost tensor flops that this workload has to spare (attention is ~4 % of a step's
 // tensor work); what mattered was removing the fp32 score tensors.
 //
-// One warp (lane 0) issues TMA and MMA, four warps own one accumulator row each (softmax, tile conversion); the phases
-// of a tile are strictly ordered by mbarriers and __syncthreads, with the next tile's operands prefetched by TMA.
+// One warp (lane 0) issues TMA and MMA; eight warps own the accumulator rows, two threads per row (softmax, tile
+// conversion).  All three kernels are software pipelines: S (and dP) have two TMEM buffers, so the tensor pipe forms
+// the scores of tile t+1 while the row threads work on tile t and applies tile t's P / dS to the accumulators while
+// they work on tile t+1; operands arrive through multi-stage TMA rings.  A tile that lies wholly inside the causal /
+// window band and holds no padding skips every per-element test; the others use one visibility bit mask per row.
 #include <cuda.h>
 #include <math.h>
 
@@ -55,31 +59,18 @@ __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
   return *reinterpret_cast<uint32_t*>(&h);
 }
 
-// Is key `kj` visible from query `qi`?
-__device__ __forceinline__ bool visible(int qi, int kj, int window) {
-  return kj <= qi && (window <= 0 || kj > qi - window);
-}
-
 // Does every query of block qb see every key of block kb (so that no per-element test is needed)?
 __device__ __forceinline__ bool tile_all_visible(int qb, int kb, int window, const uint8_t* mrow) {
   return mrow == nullptr && kb * QB + QB - 1 <= qb * QB && (window <= 0 || kb * QB > qb * QB + QB - 1 - window);
 }
 
-// First / last key block a query block needs, and first / last query block a key block is seen by (T % 128 == 0).
+// First / last key block a query block needs (T % 128 == 0).
 __device__ __forceinline__ void kv_range(int qb, int window, int& lo, int& hi) {
   hi = qb;
   lo = 0;
   if (window > 0) {
     const int first_key = qb * QB - window + 1;  // lowest key the block's first query sees
     lo = first_key > 0 ? first_key / QB : 0;
-  }
-}
-__device__ __forceinline__ void q_range(int kb, int window, int n_blk, int& lo, int& hi) {
-  lo = kb;
-  hi = n_blk - 1;
-  if (window > 0) {
-    const int last_q = kb * QB + QB - 1 + window - 1;  // highest query that still sees the block's last key
-    hi = min(n_blk - 1, last_q / QB);
   }
 }
 
@@ -121,54 +112,12 @@ __device__ __forceinline__ void mma_k_mn(uint32_t tmem_d, const uint8_t* a, cons
                    make_sw128_desc(bb + kb * 8192 + k * 2048, 16384, 1024), idesc,
                    (accumulate || kb != 0 || k != 0) ? 1u : 0u);
 }
-// D[tmem] (+)= A^T.B, A stored as [128 K rows x 128 M] (MN-major: a P / dS tile used transposed), B a TMA-loaded
-// [128 K rows x ND] tile in its MN-major view.
-template <int ND>
-__device__ __forceinline__ void mma_mn_mn(uint32_t tmem_d, const uint8_t* a, const uint8_t* b, bool accumulate) {
-  const uint32_t idesc = make_idesc_bf16(128, ND, true, true);
-  const uint32_t aa = smem_u32(a), bb = smem_u32(b);
-#pragma unroll
-  for (int kb = 0; kb < 2; ++kb)
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-      umma_bf16<1>(tmem_d, make_sw128_desc(aa + kb * 16384 + k * 2048, 8192, 1024),
-                   make_sw128_desc(bb + kb * 8192 + k * 2048, 16384, 1024), idesc,
-                   (accumulate || kb != 0 || k != 0) ? 1u : 0u);
-}
-
-// Row thread `r` writes 8 consecutive values (columns c0 .. c0+7 of its row) of a [128 x 128] bf16 tile.
-//   K-major form  (tile used as A with rows = M):        half (c0 / 64) at +16 KB, row r at r * 128 B
-//   MN-major form (tile used transposed, rows = K):      K block (r / 64) at +16 KB, column half at +8 KB, row r % 64
-// Both put 16-byte chunk c at position c ^ (row & 7) of its 128-byte line: the SWIZZLE_128B pattern TMA and UMMA use.
+// Row thread `r` writes 8 consecutive values (columns c0 .. c0+7 of its row) of a [128 x 128] bf16 tile in K-major
+// form (the tile is an A operand with rows = M): half (c0 / 64) at +16 KB, row r at r * 128 B, 16-byte chunk c at
+// position c ^ (row & 7) of its 128-byte line: the SWIZZLE_128B pattern TMA and UMMA use.
 __device__ __forceinline__ void put8_kmajor(uint8_t* tile, int r, int c0, const uint32_t w[4]) {
   uint8_t* line = tile + (c0 >> 6) * 16384 + r * 128;
   *reinterpret_cast<uint4*>(line + ((((c0 & 63) >> 3) ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
-}
-__device__ __forceinline__ void put8_mnmajor(uint8_t* tile, int r, int c0, const uint32_t w[4]) {
-  uint8_t* line = tile + (r >> 6) * 16384 + (c0 >> 6) * 8192 + (r & 63) * 128;
-  *reinterpret_cast<uint4*>(line + ((((c0 & 63) >> 3) ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
-}
-
-// The visible-and-unmasked test for 32 consecutive keys of one query row, folded into the scores:
-// v[j] = scale * log2(e) * s  (so that exp2 can be used), or -inf where the key must not be attended.
-__device__ __forceinline__ void mask_scores(float* v, int qi, int key0, const AttnParams& p, const uint8_t* mrow, float sl2,
-                                            bool all_visible) {
-  if (all_visible) {  // a tile wholly inside the causal / window band of every row of the block, no padding mask
-#pragma unroll
-    for (int j = 0; j < 32; ++j) v[j] *= sl2;
-    return;
-  }
-  uint32_t mbits = 0xffffffffu;
-  if (mrow != nullptr) {
-    const uint4 m0 = *reinterpret_cast<const uint4*>(mrow + key0), m1 = *reinterpret_cast<const uint4*>(mrow + key0 + 16);
-    const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-    mbits = 0;
-#pragma unroll
-    for (int j = 0; j < 32; ++j) mbits |= ((mw[j >> 2] >> ((j & 3) * 8)) & 0xffu) ? (1u << j) : 0u;
-  }
-#pragma unroll
-  for (int j = 0; j < 32; ++j)
-    v[j] = (visible(qi, key0 + j, p.window) && ((mbits >> j) & 1u)) ? v[j] * sl2 : -INFINITY;
 }
 
 // ------------------------------------------------------------------------------------------------ forward
@@ -190,19 +139,33 @@ __device__ __forceinline__ void key_block_flags(const uint8_t* mrow, int T, uint
   }
 }
 
-// 32 raw scores of one query row -> -inf where the key must not be attended (the forward scales afterwards).
-__device__ __forceinline__ void mask_raw(float* v, int qi, int key0, int window, const uint8_t* mrow) {
-  uint32_t mbits = 0xffffffffu;
+// Bits j (0 .. 31) with lo <= j <= hi.
+__device__ __forceinline__ uint32_t range_bits(int lo, int hi) {
+  if (hi < 0 || lo > 31 || lo > hi) return 0u;
+  lo = max(lo, 0);
+  hi = min(hi, 31);
+  return (0xffffffffu >> (31 - hi)) & (0xffffffffu << lo);
+}
+// Which of the 32 keys key0 .. key0 + 31 may query qi attend?  Causal: key <= qi; window > 0: also key > qi - window;
+// mrow != null: and the key is not padding.  One bit mask per row and chunk instead of two compares per element.
+__device__ __forceinline__ uint32_t visible_bits(int qi, int key0, int window, const uint8_t* mrow) {
+  uint32_t bits = range_bits(window > 0 ? qi - window + 1 - key0 : 0, qi - key0);
   if (mrow != nullptr) {
     const uint4 m0 = *reinterpret_cast<const uint4*>(mrow + key0), m1 = *reinterpret_cast<const uint4*>(mrow + key0 + 16);
     const uint32_t mw[8] = {m0.x, m0.y, m0.z, m0.w, m1.x, m1.y, m1.z, m1.w};
-    mbits = 0;
+    uint32_t mbits = 0;
 #pragma unroll
     for (int j = 0; j < 32; ++j) mbits |= ((mw[j >> 2] >> ((j & 3) * 8)) & 0xffu) ? (1u << j) : 0u;
+    bits &= mbits;
   }
+  return bits;
+}
+// 32 raw scores of one query row -> -inf where the key must not be attended (the caller scales afterwards).
+__device__ __forceinline__ void mask_raw(float* v, int qi, int key0, int window, const uint8_t* mrow) {
+  const uint32_t bits = visible_bits(qi, key0, window, mrow);
 #pragma unroll
   for (int j = 0; j < 32; ++j)
-    if (!(visible(qi, key0 + j, window) && ((mbits >> j) & 1u))) v[j] = -INFINITY;
+    if (!((bits >> j) & 1u)) v[j] = -INFINITY;
 }
 
 template <int DH>
@@ -428,306 +391,397 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
   delta[(static_cast<size_t>(bb) * H + h) * T + t] = acc;
 }
 
-template <int DH>
-struct BwdSmem {
-  static constexpr uint32_t TILE = QB * DH * 2;
-  // stationary pair, streamed pair, then the two [128 x 128] tiles the row threads write (P and dS)
-  static constexpr uint32_t A_OFF = 0, B_OFF = TILE, C_OFF = 2 * TILE, D_OFF = 3 * TILE, P_OFF = 4 * TILE,
-                            DS_OFF = P_OFF + 32768, BAR_OFF = DS_OFF + 32768;
-  static constexpr uint32_t FLAG_OFF = BAR_OFF + 8 * 8 + 16;  // [kMaxKeyBlocks] bytes: key block holds no padding
-  static constexpr uint32_t BYTES = 1024 + FLAG_OFF + kMaxKeyBlocks;
-};
+// The backward kernels work on 64-wide sub-tiles of the streamed operand so that everything can be double-buffered
+// inside 227 KB of shared memory and 512 TMEM columns: while the row threads turn S / dP of sub-tile t into P / dS,
+// the tensor pipe forms S / dP of sub-tile t+1 and applies sub-tile t-1's P / dS to the gradient accumulators, and TMA
+// fetches the operands of sub-tile t+2 (three-stage ring).  M = 128, N = 64 MMAs run at the full tensor rate.
+constexpr int SB = 64;  // rows of a streamed sub-tile
 
-// One thread's 128 scores and 128 dP values of a tile -> P and dS (8 columns at a time, straight into shared memory).
-// lse2 = log2-sum-exp of the row, dl = delta of the row.  kKMajor: layout of the dS tile (see put8_*).
-template <bool kWriteP, bool kKMajor>
-__device__ __forceinline__ void tile_p_ds(uint32_t taddr_s, uint32_t taddr_dp, int r, int qi, int key0, const AttnParams& p,
-                                          const uint8_t* mrow, float sl2, float lse2, float dl, uint8_t* sP, uint8_t* sDS,
-                                          bool all_visible, int half) {
-#pragma unroll 1
-  for (int c = 2 * half; c < 2 * half + 2; ++c) {
-    float v[32], g[32];
-    tmem_ld32(taddr_s + c * 32, v);
-    tmem_ld32(taddr_dp + c * 32, g);
-    tmem_ld_wait();
-    mask_scores(v, qi, key0 + c * 32, p, mrow, sl2, all_visible);
+// TMA: a [64 rows x DH cols] sub-tile as 64 x 64 boxes, column half kk at +kk * 8 KB, row r at r * 128 B (SWIZZLE_128B).
+template <int DH>
+__device__ __forceinline__ void load_sub(uint8_t* dst, const CUtensorMap* tm, uint64_t* bar, int row0, int col0) {
 #pragma unroll
-    for (int q8 = 0; q8 < 4; ++q8) {
-      uint32_t wp[4], wd[4];
+  for (int kk = 0; kk < DH / 64; ++kk) tma_load_2d(dst + kk * 8192, tm, bar, col0 + kk * 64, row0);
+}
+// D[128 x 64] = A.B^T: A a [128 x KD] K-major tile (64-column halves 16 KB apart), B a [64 x KD] K-major sub-tile
+// (halves 8 KB apart).
+template <int KD>
+__device__ __forceinline__ void mma_full_sub(uint32_t tmem_d, const uint8_t* a, const uint8_t* b) {
+  const uint32_t idesc = make_idesc_bf16(128, SB, false, false);
+  const uint32_t aa = smem_u32(a), bb = smem_u32(b);
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const int j = q8 * 8 + 2 * e;
-        const float p0 = fast_exp2(v[j] - lse2), p1 = fast_exp2(v[j + 1] - lse2);
-        wp[e] = pack2(p0, p1);
-        wd[e] = pack2(p.scale * p0 * (g[j] - dl), p.scale * p1 * (g[j + 1] - dl));
-      }
-      if (kWriteP) put8_mnmajor(sP, r, c * 32 + q8 * 8, wp);
-      if (kKMajor)
-        put8_kmajor(sDS, r, c * 32 + q8 * 8, wd);
-      else
-        put8_mnmajor(sDS, r, c * 32 + q8 * 8, wd);
+  for (int kk = 0; kk < KD / 64; ++kk)
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+      umma_bf16<1>(tmem_d, make_sw128_desc(aa + kk * 16384 + k * 32, 0, 1024), make_sw128_desc(bb + kk * 8192 + k * 32, 0, 1024),
+                   idesc, (kk != 0 || k != 0) ? 1u : 0u);
+}
+// D[128 x ND] (+)= A.B: A a [128 x 64] K-major tile the row threads wrote (one 128-byte line per row), B a TMA-loaded
+// [64 K rows x ND] sub-tile in its MN-major view (16 K rows are 2 KB apart, the 64-column halves 8 KB).
+template <int ND>
+__device__ __forceinline__ void mma_k64_mn(uint32_t tmem_d, const uint8_t* a, const uint8_t* b, bool accumulate) {
+  const uint32_t idesc = make_idesc_bf16(128, ND, false, true);
+  const uint32_t aa = smem_u32(a), bb = smem_u32(b);
+#pragma unroll
+  for (int k = 0; k < 4; ++k)
+    umma_bf16<1>(tmem_d, make_sw128_desc(aa + k * 32, 0, 1024), make_sw128_desc(bb + k * 2048, 8192, 1024), idesc,
+                 (accumulate || k != 0) ? 1u : 0u);
+}
+// Row `r` of a [128 x 64] K-major tile: 8 consecutive bf16 values at columns c0 .. c0 + 7 (c0 < 64).
+__device__ __forceinline__ void put8_row64(uint8_t* tile, int r, int c0, const uint32_t w[4]) {
+  *reinterpret_cast<uint4*>(tile + r * 128 + (((c0 >> 3) ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+}
+// Per-64-key flags: the sub-block holds no padding.  Called by the 256 row threads.
+__device__ __forceinline__ void key_sub_flags(const uint8_t* mrow, int T, uint8_t* sub_ok, int tid, int lane) {
+  for (int base = 0; base < T; base += 256 * 16) {
+    const int off = base + tid * 16;
+    bool ok = true;
+    if (off < T) {
+      const uint4 mk = *reinterpret_cast<const uint4*>(mrow + off);
+      const uint32_t w[4] = {mk.x, mk.y, mk.z, mk.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) ok = ok && (((w[e] - 0x01010101u) & ~w[e] & 0x80808080u) == 0u);
     }
+    const uint32_t bal = __ballot_sync(0xffffffffu, ok);
+    if ((lane & 3) == 0 && off < T) sub_ok[off >> 6] = (((bal >> lane) & 0xfu) == 0xfu) ? 1 : 0;
   }
-  fence_async_shared();
+}
+// O / dO / dQ-style epilogue: this thread's accumulator row (columns c = half, half + 2, ... of 32) -> bf16 -> global.
+template <int DH>
+__device__ __forceinline__ void store_acc_row(uint32_t taddr, __nv_bfloat16* dst, int half) {
+#pragma unroll 1
+  for (int c = half; c < DH / 32; c += 2) {
+    float v[32];
+    tmem_ld32(taddr + c * 32, v);
+    tmem_ld_wait();
+#pragma unroll
+    for (int q8 = 0; q8 < 4; ++q8)
+      *reinterpret_cast<uint4*>(dst + c * 32 + q8 * 8) =
+          make_uint4(pack2(v[q8 * 8], v[q8 * 8 + 1]), pack2(v[q8 * 8 + 2], v[q8 * 8 + 3]),
+                     pack2(v[q8 * 8 + 4], v[q8 * 8 + 5]), pack2(v[q8 * 8 + 6], v[q8 * 8 + 7]));
+  }
 }
 
-// Key-block stationary: dK and dV of one 128-key block of one (batch, head).
+template <int DH>
+struct BwdKvSmem {
+  static constexpr uint32_t TILE = QB * DH * 2, SUB = SB * DH * 2;
+  // stationary K and V, a three-stage ring of (Q_i, dO_i) sub-tiles, two buffers each of the P^T and dS^T tiles
+  static constexpr uint32_t K_OFF = 0, V_OFF = TILE, Q_OFF = 2 * TILE, DO_OFF = Q_OFF + 3 * SUB, PT_OFF = DO_OFF + 3 * SUB,
+                            DST_OFF = PT_OFF + 2 * 16384, BAR_OFF = DST_OFF + 2 * 16384;
+  static constexpr uint32_t STAT_OFF = BAR_OFF + 128;  // [2][64] (log2-sum-exp, delta) of the queries of a sub-tile
+  static constexpr uint32_t BYTES = 1024 + STAT_OFF + 2 * SB * 8;
+  static_assert(BYTES <= 232448, "exceeds the 227 KB of shared memory a CTA can have");
+};
+
+// Key-block stationary: dK and dV of one 128-key block of one (batch, head).  Transposed formulation: the accumulator
+// lanes are the KEYS (S^T = K.Q_i^T, dP^T = V.dO_i^T, both [128 keys x 64 queries]), so P^T and dS^T leave the row
+// threads already in the K-major layout the two gradient MMAs want as their A operand (dV += P^T.dO_i,
+// dK += dS^T.Q_i), and the per-query statistics are read from shared memory as broadcasts.
 template <int DH>
 __global__ void __launch_bounds__(kAttnThreads, 1)
     attn_bwd_kv_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                        const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
                        const AttnParams p) {
-  using L = BwdSmem<DH>;
+  using L = BwdKvSmem<DH>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sK = smem + L::A_OFF;
-  uint8_t* sV = smem + L::B_OFF;
-  uint8_t* sQ = smem + L::C_OFF;
-  uint8_t* sDO = smem + L::D_OFF;
-  uint8_t* sP = smem + L::P_OFF;
-  uint8_t* sDS = smem + L::DS_OFF;
+  uint8_t* sK = smem + L::K_OFF;
+  uint8_t* sV = smem + L::V_OFF;
+  uint8_t* sQ = smem + L::Q_OFF;    // three stages
+  uint8_t* sDO = smem + L::DO_OFF;  // three stages
+  uint8_t* sPT = smem + L::PT_OFF;  // two buffers
+  uint8_t* sDST = smem + L::DST_OFF;
   uint64_t* bar_kv = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
-  uint64_t* bar_q = bar_kv + 1;
-  uint64_t* bar_s = bar_kv + 2;
-  uint64_t* bar_o = bar_kv + 3;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_kv + 4);
+  uint64_t* bar_qd = bar_kv + 1;  // [3]
+  uint64_t* bar_s = bar_kv + 4;   // [2]
+  uint64_t* bar_o = bar_kv + 6;   // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_kv + 8);
+  float2* stat = reinterpret_cast<float2*>(smem + L::STAT_OFF);  // [2][64]
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int kb = blockIdx.x, bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
-  const int col0 = h * DH, n_blk = p.T / QB;
+  const int kb = blockIdx.x, bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;  // key block 0 sees the most queries
+  const int col0 = h * DH;
   const bool issuer = (warp == kIssuerWarp && lane == 0);
-  // Lanes 1-31 of the issuing warp take no part in mbarrier waits: spinning beside the one lane that has to issue
-  // the work the barrier is waiting for starves it.  They only join the __syncthreads.
-  const bool waits = (warp < kIssuerWarp || lane == 0);
   if (issuer) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmK);
     tma_prefetch_desc(&tmV);
     tma_prefetch_desc(&tmDO);
-    mbar_init(bar_kv, 1);
-    mbar_init(bar_q, 1);
-    mbar_init(bar_s, 1);
-    mbar_init(bar_o, 1);
+    for (int i = 0; i < 8; ++i) mbar_init(bar_kv + i, 1);
     fence_mbar_init();
   }
-  const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
-  uint8_t* blk_ok = smem + L::FLAG_OFF;
+  // query sub-blocks that see this key block
+  const int is_lo = 2 * kb;
+  int last_q = p.T - 1;
+  if (p.window > 0) last_q = min(last_q, kb * QB + QB - 1 + p.window - 1);
+  const int n = last_q / SB - is_lo + 1;
+  const size_t stat0 = static_cast<size_t>(bh) * p.T + static_cast<size_t>(is_lo) * SB;  // index of the first query's lse
+  auto load_stats = [&](int t) {  // threads 0-63: log2-sum-exp, 64-127: delta of the 64 queries of sub-tile t
+    if (threadIdx.x < 2 * SB && t < n) {
+      const int q = threadIdx.x & (SB - 1);
+      float* dst = reinterpret_cast<float*>(&stat[(t & 1) * SB + q]);
+      if (threadIdx.x < SB)
+        dst[0] = p.lse[stat0 + t * SB + q] * kLog2e;  // +inf for a row that saw no key: every p is 0
+      else
+        dst[1] = p.delta[stat0 + t * SB + q];
+    }
+  };
   if (warp == kIssuerWarp) {
     tmem_alloc<1>(tmem_slot, 512);
     tmem_relinquish<1>();
-  } else if (mrow != nullptr && warp == 0) {  // does this key block hold any padding?  (8 lanes x 16 mask bytes)
-    bool ok = true;
-    if (lane < 8) {
-      const uint4 mk = *reinterpret_cast<const uint4*>(mrow + kb * QB + lane * 16);
-      const uint32_t w[4] = {mk.x, mk.y, mk.z, mk.w};
-#pragma unroll
-      for (int e = 0; e < 4; ++e) ok = ok && (((w[e] - 0x01010101u) & ~w[e] & 0x80808080u) == 0u);
-    }
-    ok = __all_sync(0xffffffffu, ok);
-    if (lane == 0) blk_ok[0] = ok ? 1 : 0;
+  } else {
+    load_stats(0);
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_s = *tmem_slot, tmem_dp = tmem_s + 128, tmem_dv = tmem_s + 256, tmem_dk = tmem_s + 384;
-  if (mrow != nullptr && blk_ok[0]) mrow = nullptr;  // no padding among this block's keys: geometric tests only
+  const uint32_t tmem_base = *tmem_slot, tmem_dv = tmem_base + 256, tmem_dk = tmem_base + 384;
 
-  int i_lo, i_hi;
-  q_range(kb, p.window, n_blk, i_lo, i_hi);
+  auto load_qd = [&](int t) {  // (Q_i, dO_i) of sub-tile t -> ring stage t % 3
+    const int st = t % 3, row = b * p.T + (is_lo + t) * SB;
+    mbar_arrive_expect_tx(&bar_qd[st], 2 * L::SUB);
+    load_sub<DH>(sQ + st * L::SUB, &tmQ, &bar_qd[st], row, col0);
+    load_sub<DH>(sDO + st * L::SUB, &tmDO, &bar_qd[st], row, col0);
+  };
+  auto issue_s = [&](int t) {  // S^T(t) and dP^T(t) into TMEM buffer t & 1
+    const int st = t % 3;
+    mbar_wait(&bar_qd[st], (t / 3) & 1);
+    tc_fence_after();
+    mma_full_sub<DH>(tmem_base + (t & 1) * 128, sK, sQ + st * L::SUB);
+    mma_full_sub<DH>(tmem_base + (t & 1) * 128 + SB, sV, sDO + st * L::SUB);
+    umma_commit<1>(&bar_s[t & 1]);
+  };
   if (issuer) {
     mbar_arrive_expect_tx(bar_kv, 2 * L::TILE);
     load_tile<DH>(sK, &tmK, bar_kv, b * p.T + kb * QB, col0);
     load_tile<DH>(sV, &tmV, bar_kv, b * p.T + kb * QB, col0);
+    load_qd(0);
+    if (n > 1) load_qd(1);
+    mbar_wait(bar_kv, 0);
+    issue_s(0);
   }
-  const int r = threadIdx.x & 127, half = threadIdx.x >> 7;
-  const float sl2 = p.scale * kLog2e;
-  uint32_t ph = 0;
-  if (waits) mbar_wait(bar_kv, 0);
 
-  for (int i = i_lo; i <= i_hi; ++i) {
+  const int r = threadIdx.x & 127, half = (threadIdx.x >> 7) & 1;  // row threads: key row, half of the 64 query columns
+  const int kj = kb * QB + r;                                      // this thread's key
+  const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
+  const float sl2 = p.scale * kLog2e;
+  bool key_ok = true;  // a padded key is never attended: its whole row of P is 0
+  if (warp < kIssuerWarp && p.key_mask != nullptr) key_ok = p.key_mask[static_cast<size_t>(b) * p.T + kj] != 0;
+
+  for (int t = 0; t < n; ++t) {
+    const int sb = t & 1, st = t % 3;
     if (issuer) {
-      mbar_arrive_expect_tx(bar_q, 2 * L::TILE);  // the previous tile's MMAs have completed: both buffers are free
-      load_tile<DH>(sQ, &tmQ, bar_q, b * p.T + i * QB, col0);
-      load_tile<DH>(sDO, &tmDO, bar_q, b * p.T + i * QB, col0);
-      mbar_wait(bar_q, ph);
+      mbar_wait(&bar_s[sb], (t >> 1) & 1);
+      if (t >= 1) mbar_wait(&bar_o[(t - 1) & 1], ((t - 1) >> 1) & 1);  // ring stage (t + 2) % 3 is free again
+      if (t + 2 < n) load_qd(t + 2);
+      if (t + 1 < n) issue_s(t + 1);  // TMEM buffer (t + 1) & 1 was last read for sub-tile t - 1, before its sync
+    } else if (warp < kIssuerWarp) {
+      mbar_wait_poll(&bar_s[sb], (t >> 1) & 1);
       tc_fence_after();
-      mma_kk<DH>(tmem_s, sQ, sK, 128, false);     // S  = Q_i . K^T     [queries x keys]
-      mma_kk<DH>(tmem_dp, sDO, sV, 128, false);   // dP = dO_i . V^T
-      umma_commit<1>(bar_s);
-    }
-    if (waits) mbar_wait_poll(bar_s, ph);
-    tc_fence_after();
-    if (warp < kIssuerWarp) {
-      const int qi = i * QB + r;
-      const size_t sidx = static_cast<size_t>(bh) * p.T + qi;
-      const float lse = p.lse[sidx];
-      const float lse2 = lse * kLog2e;  // +inf for a row that saw no key: every p is 0
-      const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
-      tile_p_ds<true, false>(tmem_s + lane_off, tmem_dp + lane_off, r, qi, kb * QB, p, mrow, sl2, lse2, p.delta[sidx], sP,
-                             sDS, tile_all_visible(i, kb, p.window, mrow), half);
+      float v[32], g[32];
+      tmem_ld32(tmem_base + sb * 128 + lane_off + half * 32, v);
+      tmem_ld32(tmem_base + sb * 128 + SB + lane_off + half * 32, g);
+      tmem_ld_wait();
+      const int q0 = (is_lo + t) * SB + half * 32;  // first query of this thread's 32 columns
+      // every query of the sub-tile sees every key of the block?  (then only the padding flag of the key matters)
+      const bool all_vis = (is_lo + t) * SB >= kb * QB + QB - 1 &&
+                           (p.window <= 0 || (is_lo + t) * SB + SB - 1 - p.window < kb * QB);
+      const float2* sq = stat + sb * SB + half * 32;
+      // queries q0 + c that see key kj: q >= kj, and q < kj + window for a sliding window; none if the key is padding
+      uint32_t bits = 0xffffffffu;
+      if (!all_vis) bits = range_bits(kj - q0, p.window > 0 ? kj + p.window - 1 - q0 : 31);
+      if (!key_ok) bits = 0u;
+      uint32_t wp[16], wd[16];
+#pragma unroll
+      for (int e = 0; e < 16; ++e) {
+        const float2 s0 = sq[2 * e], s1 = sq[2 * e + 1];  // (log2-sum-exp, delta) of the two queries: broadcast reads
+        float p0 = fast_exp2(fmaf(v[2 * e], sl2, -s0.x)), p1 = fast_exp2(fmaf(v[2 * e + 1], sl2, -s1.x));
+        if (!((bits >> (2 * e)) & 1u)) p0 = 0.f;
+        if (!((bits >> (2 * e + 1)) & 1u)) p1 = 0.f;
+        wp[e] = pack2(p0, p1);
+        wd[e] = pack2(p.scale * p0 * (g[2 * e] - s0.y), p.scale * p1 * (g[2 * e + 1] - s1.y));
+      }
+      if (t >= 2) mbar_wait_poll(&bar_o[sb], ((t - 2) >> 1) & 1);  // the MMAs that read these two buffers are done
+      uint8_t* pt = sPT + sb * 16384;
+      uint8_t* dst = sDST + sb * 16384;
+#pragma unroll
+      for (int q8 = 0; q8 < 4; ++q8) {
+        put8_row64(pt, r, half * 32 + q8 * 8, &wp[q8 * 4]);
+        put8_row64(dst, r, half * 32 + q8 * 8, &wd[q8 * 4]);
+      }
+      fence_async_shared();
+      load_stats(t + 1);  // its buffer was last read for sub-tile t - 1
     }
     tc_fence_before();
     __syncthreads();
     if (issuer) {
       tc_fence_after();
-      mma_mn_mn<DH>(tmem_dv, sP, sDO, i != i_lo);  // dV += P^T . dO_i
-      mma_mn_mn<DH>(tmem_dk, sDS, sQ, i != i_lo);  // dK += dS^T . Q_i
-      umma_commit<1>(bar_o);
+      mma_k64_mn<DH>(tmem_dv, sPT + sb * 16384, sDO + st * L::SUB, t != 0);  // dV += P^T . dO_i
+      mma_k64_mn<DH>(tmem_dk, sDST + sb * 16384, sQ + st * L::SUB, t != 0);  // dK += dS^T . Q_i
+      umma_commit<1>(&bar_o[sb]);
     }
-    if (waits) mbar_wait_poll(bar_o, ph);
-    tc_fence_after();
-    ph ^= 1;
   }
 
   if (warp < kIssuerWarp) {  // accumulator lane = key row
-    const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
-    const size_t row = static_cast<size_t>(b) * p.T + kb * QB + r;
-#pragma unroll 1
-    for (int which = 0; which < 2; ++which) {
-      __nv_bfloat16* dst = (which == 0 ? p.out0 : p.out1) + row * (p.H * DH) + col0;
-      const uint32_t taddr = (which == 0 ? tmem_dk : tmem_dv) + lane_off;
-#pragma unroll 1
-      for (int c = half; c < DH / 32; c += 2) {
-        float v[32];
-        tmem_ld32(taddr + c * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int q8 = 0; q8 < 4; ++q8)
-          *reinterpret_cast<uint4*>(dst + c * 32 + q8 * 8) =
-              make_uint4(pack2(v[q8 * 8], v[q8 * 8 + 1]), pack2(v[q8 * 8 + 2], v[q8 * 8 + 3]),
-                         pack2(v[q8 * 8 + 4], v[q8 * 8 + 5]), pack2(v[q8 * 8 + 6], v[q8 * 8 + 7]));
-      }
-    }
+    mbar_wait_poll(&bar_o[(n - 1) & 1], ((n - 1) >> 1) & 1);  // the last pair of MMAs (they complete in order)
+    tc_fence_after();
+    const size_t row = static_cast<size_t>(b) * p.T + kj;
+    store_acc_row<DH>(tmem_dk + lane_off, p.out0 + row * (p.H * DH) + col0, half);
+    store_acc_row<DH>(tmem_dv + lane_off, p.out1 + row * (p.H * DH) + col0, half);
   }
   tc_fence_before();
   __syncthreads();
   if (warp == kIssuerWarp) {
     tc_fence_after();
-    tmem_dealloc<1>(tmem_s, 512);
+    tmem_dealloc<1>(tmem_base, 512);
   }
 }
 
-// Query-block stationary: dQ of one 128-query block of one (batch, head).
+template <int DH>
+struct BwdQSmem {
+  static constexpr uint32_t TILE = QB * DH * 2, SUB = SB * DH * 2;
+  // stationary Q and dO, a three-stage ring of (K_j, V_j) sub-tiles, two buffers of the dS tile
+  static constexpr uint32_t Q_OFF = 0, DO_OFF = TILE, K_OFF = 2 * TILE, V_OFF = K_OFF + 3 * SUB, DS_OFF = V_OFF + 3 * SUB,
+                            BAR_OFF = DS_OFF + 2 * 16384;
+  static constexpr uint32_t FLAG_OFF = BAR_OFF + 128;  // [2 * kMaxKeyBlocks] bytes: 64-key sub-block holds no padding
+  static constexpr uint32_t BYTES = 1024 + FLAG_OFF + 2 * kMaxKeyBlocks;
+  static_assert(BYTES <= 232448, "exceeds the 227 KB of shared memory a CTA can have");
+};
+
+// Query-block stationary: dQ of one 128-query block of one (batch, head), over 64-key sub-tiles.
 template <int DH>
 __global__ void __launch_bounds__(kAttnThreads, 1)
     attn_bwd_q_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
                       const __grid_constant__ CUtensorMap tmV, const __grid_constant__ CUtensorMap tmDO,
                       const AttnParams p) {
-  using L = BwdSmem<DH>;
+  using L = BwdQSmem<DH>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* sQ = smem + L::A_OFF;
-  uint8_t* sDO = smem + L::B_OFF;
-  uint8_t* sK = smem + L::C_OFF;
-  uint8_t* sV = smem + L::D_OFF;
-  uint8_t* sDS = smem + L::DS_OFF;
+  uint8_t* sQ = smem + L::Q_OFF;
+  uint8_t* sDO = smem + L::DO_OFF;
+  uint8_t* sK = smem + L::K_OFF;  // three stages
+  uint8_t* sV = smem + L::V_OFF;  // three stages
+  uint8_t* sDS = smem + L::DS_OFF;  // two buffers
   uint64_t* bar_q = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
-  uint64_t* bar_kv = bar_q + 1;
-  uint64_t* bar_s = bar_q + 2;
-  uint64_t* bar_o = bar_q + 3;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_q + 4);
+  uint64_t* bar_kv = bar_q + 1;  // [3]
+  uint64_t* bar_s = bar_q + 4;   // [2]
+  uint64_t* bar_o = bar_q + 6;   // [2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_q + 8);
+  uint8_t* sub_ok = smem + L::FLAG_OFF;
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int qb = static_cast<int>(gridDim.x) - 1 - static_cast<int>(blockIdx.x);  // longest key ranges first
   const int bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
   const int col0 = h * DH;
   const bool issuer = (warp == kIssuerWarp && lane == 0);
-  // Lanes 1-31 of the issuing warp take no part in mbarrier waits: spinning beside the one lane that has to issue
-  // the work the barrier is waiting for starves it.  They only join the __syncthreads.
-  const bool waits = (warp < kIssuerWarp || lane == 0);
+  const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
   if (issuer) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmK);
     tma_prefetch_desc(&tmV);
     tma_prefetch_desc(&tmDO);
-    mbar_init(bar_q, 1);
-    mbar_init(bar_kv, 1);
-    mbar_init(bar_s, 1);
-    mbar_init(bar_o, 1);
+    for (int i = 0; i < 8; ++i) mbar_init(bar_q + i, 1);
     fence_mbar_init();
   }
-  const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
-  uint8_t* blk_ok = smem + L::FLAG_OFF;
   if (warp == kIssuerWarp) {
     tmem_alloc<1>(tmem_slot, 512);
     tmem_relinquish<1>();
   } else if (mrow != nullptr) {
-    key_block_flags(mrow, p.T, blk_ok, threadIdx.x, lane);
+    key_sub_flags(mrow, p.T, sub_ok, threadIdx.x, lane);
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_s = *tmem_slot, tmem_dp = tmem_s + 128, tmem_dq = tmem_s + 256;
+  const uint32_t tmem_base = *tmem_slot, tmem_dq = tmem_base + 256;
 
-  int j_lo, j_hi;
-  kv_range(qb, p.window, j_lo, j_hi);
+  // key sub-blocks this query block sees
+  int first_key = 0;
+  if (p.window > 0) first_key = max(0, qb * QB - p.window + 1);
+  const int js_lo = first_key / SB, n = 2 * qb + 1 - js_lo + 1;
+  auto load_kv = [&](int t) {  // (K_j, V_j) of sub-tile t -> ring stage t % 3
+    const int st = t % 3, row = b * p.T + (js_lo + t) * SB;
+    mbar_arrive_expect_tx(&bar_kv[st], 2 * L::SUB);
+    load_sub<DH>(sK + st * L::SUB, &tmK, &bar_kv[st], row, col0);
+    load_sub<DH>(sV + st * L::SUB, &tmV, &bar_kv[st], row, col0);
+  };
+  auto issue_s = [&](int t) {  // S(t) = Q.K_j^T and dP(t) = dO.V_j^T into TMEM buffer t & 1
+    const int st = t % 3;
+    mbar_wait(&bar_kv[st], (t / 3) & 1);
+    tc_fence_after();
+    mma_full_sub<DH>(tmem_base + (t & 1) * 128, sQ, sK + st * L::SUB);
+    mma_full_sub<DH>(tmem_base + (t & 1) * 128 + SB, sDO, sV + st * L::SUB);
+    umma_commit<1>(&bar_s[t & 1]);
+  };
   if (issuer) {
     mbar_arrive_expect_tx(bar_q, 2 * L::TILE);
     load_tile<DH>(sQ, &tmQ, bar_q, b * p.T + qb * QB, col0);
     load_tile<DH>(sDO, &tmDO, bar_q, b * p.T + qb * QB, col0);
+    load_kv(0);
+    if (n > 1) load_kv(1);
+    mbar_wait(bar_q, 0);
+    issue_s(0);
   }
-  const int r = threadIdx.x & 127, half = threadIdx.x >> 7, qi = qb * QB + r;
+
+  const int r = threadIdx.x & 127, half = (threadIdx.x >> 7) & 1, qi = qb * QB + r;
+  const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
   const float sl2 = p.scale * kLog2e;
   float lse2 = 0.f, dl = 0.f;
   if (warp < kIssuerWarp) {
     const size_t sidx = static_cast<size_t>(bh) * p.T + qi;
-    lse2 = p.lse[sidx] * kLog2e;
+    lse2 = p.lse[sidx] * kLog2e;  // +inf for a row that saw no key: every p is 0
     dl = p.delta[sidx];
   }
-  uint32_t ph = 0;
-  if (waits) mbar_wait(bar_q, 0);
 
-  for (int j = j_lo; j <= j_hi; ++j) {
+  for (int t = 0; t < n; ++t) {
+    const int sb = t & 1, st = t % 3, js = js_lo + t;
     if (issuer) {
-      mbar_arrive_expect_tx(bar_kv, 2 * L::TILE);
-      load_tile<DH>(sK, &tmK, bar_kv, b * p.T + j * QB, col0);
-      load_tile<DH>(sV, &tmV, bar_kv, b * p.T + j * QB, col0);
-      mbar_wait(bar_kv, ph);
+      mbar_wait(&bar_s[sb], (t >> 1) & 1);
+      if (t >= 1) mbar_wait(&bar_o[(t - 1) & 1], ((t - 1) >> 1) & 1);  // ring stage (t + 2) % 3 is free again
+      if (t + 2 < n) load_kv(t + 2);
+      if (t + 1 < n) issue_s(t + 1);
+    } else if (warp < kIssuerWarp) {
+      mbar_wait_poll(&bar_s[sb], (t >> 1) & 1);
       tc_fence_after();
-      mma_kk<DH>(tmem_s, sQ, sK, 128, false);    // S  = Q . K_j^T
-      mma_kk<DH>(tmem_dp, sDO, sV, 128, false);  // dP = dO . V_j^T
-      umma_commit<1>(bar_s);
-    }
-    if (waits) mbar_wait_poll(bar_s, ph);
-    tc_fence_after();
-    if (warp < kIssuerWarp) {
-      const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
-      const uint8_t* mr = (mrow != nullptr && !blk_ok[j]) ? mrow : nullptr;
-      tile_p_ds<false, true>(tmem_s + lane_off, tmem_dp + lane_off, r, qi, j * QB, p, mr, sl2, lse2, dl, nullptr, sDS,
-                             tile_all_visible(qb, j, p.window, mr), half);
+      float v[32], g[32];
+      tmem_ld32(tmem_base + sb * 128 + lane_off + half * 32, v);
+      tmem_ld32(tmem_base + sb * 128 + SB + lane_off + half * 32, g);
+      tmem_ld_wait();
+      const int key0 = js * SB + half * 32;
+      const uint8_t* mr = (mrow != nullptr && !sub_ok[js]) ? mrow : nullptr;
+      const bool all_vis = mr == nullptr && js * SB + SB - 1 <= qb * QB &&
+                           (p.window <= 0 || js * SB > qb * QB + QB - 1 - p.window);
+      if (!all_vis) mask_raw(v, qi, key0, p.window, mr);  // -inf where the key must not be attended -> p = 0
+      uint32_t wd[16];
+#pragma unroll
+      for (int e = 0; e < 16; ++e) {
+        const float p0 = fast_exp2(fmaf(v[2 * e], sl2, -lse2)), p1 = fast_exp2(fmaf(v[2 * e + 1], sl2, -lse2));
+        wd[e] = pack2(p.scale * p0 * (g[2 * e] - dl), p.scale * p1 * (g[2 * e + 1] - dl));
+      }
+      if (t >= 2) mbar_wait_poll(&bar_o[sb], ((t - 2) >> 1) & 1);  // the MMA that read this dS buffer is done
+      uint8_t* ds = sDS + sb * 16384;
+#pragma unroll
+      for (int q8 = 0; q8 < 4; ++q8) put8_row64(ds, r, half * 32 + q8 * 8, &wd[q8 * 4]);
+      fence_async_shared();
     }
     tc_fence_before();
     __syncthreads();
     if (issuer) {
       tc_fence_after();
-      mma_k_mn<DH>(tmem_dq, sDS, sK, j != j_lo);  // dQ += dS . K_j
-      umma_commit<1>(bar_o);
+      mma_k64_mn<DH>(tmem_dq, sDS + sb * 16384, sK + st * L::SUB, t != 0);  // dQ += dS . K_j
+      umma_commit<1>(&bar_o[sb]);
     }
-    if (waits) mbar_wait_poll(bar_o, ph);
-    tc_fence_after();
-    ph ^= 1;
   }
 
   if (warp < kIssuerWarp) {
-    const uint32_t taddr = tmem_dq + (static_cast<uint32_t>((warp & 3) * 32) << 16);
-    __nv_bfloat16* dst = p.out0 + (static_cast<size_t>(b) * p.T + qi) * (p.H * DH) + col0;
-#pragma unroll 1
-    for (int c = half; c < DH / 32; c += 2) {
-      float v[32];
-      tmem_ld32(taddr + c * 32, v);
-      tmem_ld_wait();
-#pragma unroll
-      for (int q8 = 0; q8 < 4; ++q8)
-        *reinterpret_cast<uint4*>(dst + c * 32 + q8 * 8) =
-            make_uint4(pack2(v[q8 * 8], v[q8 * 8 + 1]), pack2(v[q8 * 8 + 2], v[q8 * 8 + 3]),
-                       pack2(v[q8 * 8 + 4], v[q8 * 8 + 5]), pack2(v[q8 * 8 + 6], v[q8 * 8 + 7]));
-    }
+    mbar_wait_poll(&bar_o[(n - 1) & 1], ((n - 1) >> 1) & 1);
+    tc_fence_after();
+    store_acc_row<DH>(tmem_dq + lane_off, p.out0 + (static_cast<size_t>(b) * p.T + qi) * (p.H * DH) + col0, half);
   }
   tc_fence_before();
   __syncthreads();
   if (warp == kIssuerWarp) {
     tc_fence_after();
-    tmem_dealloc<1>(tmem_s, 512);
+    tmem_dealloc<1>(tmem_base, 512);
   }
 }
 
@@ -780,8 +834,8 @@ int run_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
   if (int rc = attn_tmap(&tk, k, B, p.T, p.H, DH)) return rc;
   if (int rc = attn_tmap(&tv, v, B, p.T, p.H, DH)) return rc;
   if (int rc = attn_tmap(&tdo, d_o, B, p.T, p.H, DH)) return rc;
-  if (int rc = set_smem(attn_bwd_kv_kernel<DH>, BwdSmem<DH>::BYTES)) return rc;
-  if (int rc = set_smem(attn_bwd_q_kernel<DH>, BwdSmem<DH>::BYTES)) return rc;
+  if (int rc = set_smem(attn_bwd_kv_kernel<DH>, BwdKvSmem<DH>::BYTES)) return rc;
+  if (int rc = set_smem(attn_bwd_q_kernel<DH>, BwdQSmem<DH>::BYTES)) return rc;
   ftk::TimelineScope tl_(FTK_TL_ATTN_BWD, st);
   const int n = B * p.T * p.H;
   attn_delta_kernel<DH><<<(n + 255) / 256, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(o),
@@ -791,11 +845,11 @@ int run_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
   const dim3 grid(p.T / QB, B * p.H);
   p.out0 = static_cast<__nv_bfloat16*>(dk);
   p.out1 = static_cast<__nv_bfloat16*>(dv);
-  attn_bwd_kv_kernel<DH><<<grid, kAttnThreads, BwdSmem<DH>::BYTES, st>>>(tq, tk, tv, tdo, p);
+  attn_bwd_kv_kernel<DH><<<grid, kAttnThreads, BwdKvSmem<DH>::BYTES, st>>>(tq, tk, tv, tdo, p);
   FTK_CUDA_CHECK(cudaGetLastError());
   p.out0 = static_cast<__nv_bfloat16*>(dq);
   p.out1 = nullptr;
-  attn_bwd_q_kernel<DH><<<grid, kAttnThreads, BwdSmem<DH>::BYTES, st>>>(tq, tk, tv, tdo, p);
+  attn_bwd_q_kernel<DH><<<grid, kAttnThreads, BwdQSmem<DH>::BYTES, st>>>(tq, tk, tv, tdo, p);
   FTK_CUDA_CHECK(cudaGetLastError());
   return FTK_OK;
 }

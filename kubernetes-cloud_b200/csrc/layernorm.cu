@@ -65,15 +65,18 @@ __global__ void __launch_bounds__(kFwdWarps * 32)
   const int64_t row = static_cast<int64_t>(blockIdx.x) * kFwdWarps + warp;
   if (row >= M) return;
   const __nv_bfloat16* xr = x + row * D;
-  float v[NC][8];
+  uint4 raw[NC];  // the row stays packed (4 registers per 8 values): more warps per SM hide more of the HBM latency
+#pragma unroll
+  for (int c = 0; c < NC; ++c)
+    if (c * 256 + lane * 8 < D) raw[c] = ld_stream(xr + c * 256 + lane * 8);
   float s = 0.f;
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
-    const int col = c * 256 + lane * 8;
-    if (col < D) {
-      unpack8(ld_stream(xr + col), v[c]);
+    if (c * 256 + lane * 8 < D) {
+      float v[8];
+      unpack8(raw[c], v);
 #pragma unroll
-      for (int e = 0; e < 8; ++e) s += v[c][e];
+      for (int e = 0; e < 8; ++e) s += v[e];
     }
   }
   const float mu = warp_sum(s) / static_cast<float>(D);
@@ -81,9 +84,11 @@ __global__ void __launch_bounds__(kFwdWarps * 32)
 #pragma unroll
   for (int c = 0; c < NC; ++c) {
     if (c * 256 + lane * 8 < D) {
+      float v[8];
+      unpack8(raw[c], v);
 #pragma unroll
       for (int e = 0; e < 8; ++e) {
-        const float d = v[c][e] - mu;
+        const float d = v[e] - mu;
         q += d * d;
       }
     }
@@ -94,7 +99,8 @@ __global__ void __launch_bounds__(kFwdWarps * 32)
   for (int c = 0; c < NC; ++c) {
     const int col = c * 256 + lane * 8;
     if (col < D) {
-      float g[8], bt[8], o[8];
+      float v[8], g[8], bt[8], o[8];
+      unpack8(raw[c], v);
       unpack8(__ldg(reinterpret_cast<const uint4*>(gamma + col)), g);
       if (beta != nullptr) {
         unpack8(__ldg(reinterpret_cast<const uint4*>(beta + col)), bt);
@@ -103,7 +109,7 @@ __global__ void __launch_bounds__(kFwdWarps * 32)
         for (int e = 0; e < 8; ++e) bt[e] = 0.f;
       }
 #pragma unroll
-      for (int e = 0; e < 8; ++e) o[e] = fmaf((v[c][e] - mu) * rs, g[e], bt[e]);
+      for (int e = 0; e < 8; ++e) o[e] = fmaf((v[e] - mu) * rs, g[e], bt[e]);
       *reinterpret_cast<uint4*>(yr + col) = pack8(o);
     }
   }
@@ -212,7 +218,8 @@ __global__ void __launch_bounds__(256) ln_bwd_finalize_kernel(const float* __res
   const int col = blockIdx.x * 32 + cx;
   float a = 0.f, b = 0.f;
   if (col < D) {
-    for (int i = ry; i < n_blocks; i += 8) {
+#pragma unroll 8
+    for (int i = ry; i < n_blocks; i += 8) {  // fixed order per thread; unrolled so that the loads overlap
       a += part[static_cast<size_t>(i) * 2 * D + col];
       b += part[static_cast<size_t>(i) * 2 * D + D + col];
     }
@@ -311,7 +318,12 @@ extern "C" int ftk_layernorm_bwd(const void* dY, const void* X, const void* gamm
   const int threads = D / 8;
   const size_t smem = static_cast<size_t>(2) * (threads / 32) * 2 * kBwdRows * sizeof(float);
   ftk::TimelineScope tl_(FTK_TL_LAYERNORM_BWD, st);
-  if (threads <= 512)
+  if (threads <= 256)
+    ln_bwd_kernel<kBwdRows, 256><<<n_blocks, threads, smem, st>>>(
+        static_cast<const __nv_bfloat16*>(dY), static_cast<const __nv_bfloat16*>(X),
+        static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<const __nv_bfloat16*>(dx_add),
+        static_cast<__nv_bfloat16*>(dX), part, M, D, rpb);
+  else if (threads <= 512)
     ln_bwd_kernel<kBwdRows, 512><<<n_blocks, threads, smem, st>>>(
         static_cast<const __nv_bfloat16*>(dY), static_cast<const __nv_bfloat16*>(X),
         static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<const __nv_bfloat16*>(dx_add),

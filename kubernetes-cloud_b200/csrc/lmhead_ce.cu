@@ -513,14 +513,34 @@ struct LinearEpi {
     st.row = row;
   }
   static __device__ __forceinline__ void set_split(State&, const Params&, int) {}
+  // The side inputs of one 32-column chunk of this thread's row (mul_pre and residual, 64 bytes each).  They are
+  // fetched one chunk ahead: a thread reads its own row, so these loads are latency-, not bandwidth-bound, and left in
+  // the chunk's dependency chain they stretch the epilogue past the MMAs of the next tile.
+  struct Side {
+    uint4 m[4], r[4];
+  };
+  static __device__ __forceinline__ void fetch(Side& sd, const State& st, const Params& p, int col0) {
+    if (st.row >= p.rows || col0 >= p.cols) return;
+    const size_t off = static_cast<size_t>(st.row) * p.ld + col0;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      if (col0 + q * 8 >= p.cols) break;
+      if (p.mul_pre != nullptr) sd.m[q] = *(reinterpret_cast<const uint4*>(p.mul_pre + off) + q);
+      if (p.residual != nullptr) sd.r[q] = *(reinterpret_cast<const uint4*>(p.residual + off) + q);
+    }
+  }
   template <int BN>
   static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0, const EpiCtx&) {
+    Side nxt = {};
+    fetch(nxt, st, p, n0);
 #pragma unroll 1
     for (int c = 0; c < BN / 32; ++c) {
       const int col0 = n0 + c * 32;
       if (col0 >= p.cols) break;  // warp-uniform
       float v[32];
       tmem_ld32(taddr + c * 32, v);
+      const Side cur = nxt;
+      if (c + 1 < BN / 32) fetch(nxt, st, p, col0 + 32);
       tmem_ld_wait();
       if (st.row < p.rows) {  // no `continue`: the next tcgen05.ld needs a converged warp
         const size_t off = static_cast<size_t>(st.row) * p.ld + col0;
@@ -539,8 +559,7 @@ struct LinearEpi {
             }
           }
           if (p.mul_pre != nullptr) {
-            const uint4 pw = *(reinterpret_cast<const uint4*>(p.mul_pre + off) + q);
-            const uint32_t p4[4] = {pw.x, pw.y, pw.z, pw.w};
+            const uint32_t p4[4] = {cur.m[q].x, cur.m[q].y, cur.m[q].z, cur.m[q].w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&p4[e]);
@@ -556,8 +575,7 @@ struct LinearEpi {
             for (int e = 0; e < 8; ++e) x[e] = gelu_new(x[e]);
           }
           if (p.residual != nullptr) {
-            const uint4 rw = *(reinterpret_cast<const uint4*>(p.residual + off) + q);
-            const uint32_t r4[4] = {rw.x, rw.y, rw.z, rw.w};
+            const uint32_t r4[4] = {cur.r[q].x, cur.r[q].y, cur.r[q].z, cur.r[q].w};
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&r4[e]);

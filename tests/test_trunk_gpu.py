@@ -267,19 +267,28 @@ def test_attention_rows_without_keys_and_padding_inside_a_block(cuda_dev):
 
 
 def test_attention_long_sequence_is_deterministic(cuda_dev):
-    """T = 2048 (the bench context): many tiles through the double-buffered score pipeline; two runs agree bit for
-    bit and the last query block matches the fp32 restatement."""
+    """T = 2048 (the bench context): many tiles through the double-buffered score pipelines and the three-stage operand
+    rings of the backward kernels; two runs agree bit for bit, and output and gradients match the fp32 restatement."""
     from kubernetes_cloud_b200 import trunk
     B, T, H, dh = 1, 2048, 2, 128
     g = torch.Generator().manual_seed(21)
-    q, k, v = ((torch.randn(B, T, H * dh, generator=g) * s).to(torch.bfloat16).cuda() for s in (0.3, 0.3, 1.0))
+    q, k, v, d_o = ((torch.randn(B, T, H * dh, generator=g) * s).to(torch.bfloat16) for s in (0.3, 0.3, 1.0, 1.0))
     for window in (0, 256):
-        o1 = trunk.attention(q, k, v, None, H, window, 1.0)
-        o2 = trunk.attention(q, k, v, None, H, window, 1.0)
+        ref = [t.float().requires_grad_(True) for t in (q, k, v)]
+        o_ref = attention_reference(*ref, None, H, window, 1.0)
+        o_ref.backward(d_o.float())
+        runs = []
+        for _ in range(2):
+            got = [t.cuda().requires_grad_(True) for t in (q, k, v)]
+            o = trunk.attention(*got, None, H, window, 1.0)
+            o.backward(d_o.cuda())
+            runs.append((o.detach(), *(t.grad for t in got)))
         torch.cuda.synchronize()
-        assert torch.equal(o1, o2)
-        o_ref = attention_reference(q.cpu(), k.cpu(), v.cpu(), None, H, window, 1.0)
-        assert O.rel_err(o1.float().cpu(), o_ref) < RTOL
+        for a, c in zip(*runs):
+            assert torch.equal(a, c)
+        assert O.rel_err(runs[0][0].float().cpu(), o_ref) < RTOL
+        for name, a, r in zip(("dq", "dk", "dv"), runs[0][1:], ref):
+            assert O.rel_err(a.float().cpu(), r.grad) < 1.5e-2, (name, window)
 
 
 @pytest.mark.parametrize("fuse_blocks", [False, True])
