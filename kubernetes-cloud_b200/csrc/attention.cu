@@ -19,6 +19,9 @@
 // The extra S / dP recomputations cost tensor flops that this workload has to spare (attention is ~4 % of a step's
 // tensor work); what mattered was removing the fp32 score tensors.
 //
+// Every mbarrier wait here is a pure poll (mbarrier.test_wait): the suspending form (try_wait + NANOSLEEP.SYNCS) wakes
+// up late enough to stall these pipelines on their single issuing thread.
+//
 // One warp (lane 0) issues TMA and MMA; eight warps own the accumulator rows, two threads per row (softmax, tile
 // conversion).  All three kernels are software pipelines: S (and dP) have two TMEM buffers, so the tensor pipe forms
 // the scores of tile t+1 while the row threads work on tile t and applies tile t's P / dS to the accumulators while
@@ -39,6 +42,7 @@ constexpr int QB = 128;            // rows of a block (queries or keys) = TMEM l
 // per scheduler nothing hid the TMEM-load and MUFU latencies (ncu: issue slots 22 % busy, tensor pipe 15 %).
 // Warp 8: TMA + MMA issue (lane 0), TMEM allocation.
 constexpr int kAttnThreads = 288;
+constexpr int kRowThreads = 256;
 constexpr int kIssuerWarp = 8;
 constexpr float kLog2e = 1.4426950408889634f;
 constexpr float kLn2 = 0.6931471805599453f;
@@ -47,7 +51,7 @@ constexpr int kMaxKeyBlocks = 256;  // per-key-block padding flags kept in share
 struct AttnParams {
   const uint8_t* key_mask;  // [batch * T] (1 = may be attended) or null
   float* lse;               // [batch * heads * T]
-  const float* delta;       // backward: rowsum(dO * O) [batch * heads * T]
+  const float2* stats;      // backward: (lse * log2(e), rowsum(dO * O)) [batch * heads * T]
   __nv_bfloat16* out0;      // forward: O; kv kernel: dK; q kernel: dQ     ([batch * T, heads * head_dim])
   __nv_bfloat16* out1;      // kv kernel: dV
   int T, H, window;         // window > 0: key j is visible from query i iff i - window < j <= i; 0: plain causal
@@ -74,6 +78,65 @@ __device__ __forceinline__ void kv_range(int qb, int window, int& lo, int& hi) {
   }
 }
 
+// The MMA-issuing code is written for the compiler's uniform datapath: the whole issuing warp runs it in lockstep on
+// warp-uniform values and one elected lane executes the tcgen05 / TMA instructions.  Issued from a divergent
+// `if (lane == 0)` region with per-thread values, every tcgen05.mma cost ~90 cycles of operand shuffling
+// (ELECT / R2UR.BROADCAST loops), more than the MMA itself takes to execute.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P1;\n\telect.sync _|P1, 0xffffffff;\n\tselp.u32 %0, 1, 0, P1;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
+// The instructions one lane issues for the warp, each predicated on elect.sync inside its own asm block: the form the
+// compiler turns into ELECT + one predicated UTCHMMA / UTMALDG / UTCBAR (inside an ordinary `if (lane == 0)` region it
+// wraps every one of them in a loop over the active lanes).  Call them from the whole, converged issuing warp.
+__device__ __forceinline__ void e_umma_bf16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\tsetp.ne.b32 p, %4, 0;\n\telect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void e_umma_commit(uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(smem_u32(bar))
+      : "memory");
+}
+__device__ __forceinline__ void e_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\t"
+      "@q mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n\t}" ::"r"(smem_u32(bar)),
+      "r"(bytes)
+      : "memory");
+}
+__device__ __forceinline__ void e_tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\t"
+      "@q cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n\t}" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void e_bulk_load_1d(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile(
+      "{\n\t.reg .pred q;\n\telect.sync _|q, 0xffffffff;\n\t"
+      "@q cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n\t}" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar))
+      : "memory");
+}
+
+// A SWIZZLE_128B shared-memory descriptor (ftk_ptx.cuh: make_sw128_desc) as its two words; stepping through a tile
+// only adds (byte offset >> 4) to the low word (no carry: shared-memory addresses stay below 2^18).
+__device__ __forceinline__ uint32_t desc_lo(uint32_t smem_addr, uint32_t lbo_bytes) {
+  return ((smem_addr >> 4) & 0x3FFFu) | (((lbo_bytes >> 4) & 0x3FFFu) << 16);
+}
+constexpr uint32_t kDescHi = ((1024u >> 4) & 0x3FFFu) | (1u << 14) | (2u << 29);  // SBO 1024, version 1, SWIZZLE_128B
+__device__ __forceinline__ uint64_t desc_at(uint32_t lo, uint32_t byte_off) {
+  return (static_cast<uint64_t>(kDescHi) << 32) | (lo + (byte_off >> 4));
+}
+
 // TMA: a [128 rows x DH cols] tile as 64 x 64 boxes: column half kk at +kk * 16 KB, row r at r * 128 B inside it
 // (SWIZZLE_128B).  That is the K-major operand layout (rows = M or N, head_dim = K).  The same bytes serve as an
 // MN-major operand (rows = K, head_dim = M or N): K block kb (64 rows) starts at +kb * 8 KB, 16 K rows are 2 KB apart,
@@ -83,33 +146,32 @@ __device__ __forceinline__ void load_tile(uint8_t* dst, const CUtensorMap* tm, u
 #pragma unroll
   for (int kk = 0; kk < DH / 64; ++kk)
 #pragma unroll
-    for (int rr = 0; rr < 2; ++rr) tma_load_2d(dst + kk * 16384 + rr * 8192, tm, bar, col0 + kk * 64, row0 + rr * 64);
+    for (int rr = 0; rr < 2; ++rr) e_tma_load_2d(dst + kk * 16384 + rr * 8192, tm, bar, col0 + kk * 64, row0 + rr * 64);
 }
 
 // D[tmem] (+)= A.B^T with both operands K-major tiles of [128 rows x KD] (KD = 64 or 128): S = Q.K^T, dP = dO.V^T.
 template <int KD>
 __device__ __forceinline__ void mma_kk(uint32_t tmem_d, const uint8_t* a, const uint8_t* b, uint32_t n, bool accumulate) {
   const uint32_t idesc = make_idesc_bf16(128, n, false, false);
-  const uint32_t aa = smem_u32(a), bb = smem_u32(b);
+  const uint32_t aa = desc_lo(smem_u32(a), 0), bb = desc_lo(smem_u32(b), 0);
 #pragma unroll
   for (int kk = 0; kk < KD / 64; ++kk)
 #pragma unroll
     for (int k = 0; k < 4; ++k)
-      umma_bf16<1>(tmem_d, make_sw128_desc(aa + kk * 16384 + k * 32, 0, 1024), make_sw128_desc(bb + kk * 16384 + k * 32, 0, 1024),
-                   idesc, (accumulate || kk != 0 || k != 0) ? 1u : 0u);
+      e_umma_bf16(tmem_d, desc_at(aa, kk * 16384 + k * 32), desc_at(bb, kk * 16384 + k * 32), idesc,
+                   (accumulate || kk != 0 || k != 0) ? 1u : 0u);
 }
 // D[tmem] (+)= A.B, A K-major [128 x 128] (a P / dS tile written by the row threads), B a TMA-loaded [128 K rows x ND]
 // tile in its MN-major view.
 template <int ND>
 __device__ __forceinline__ void mma_k_mn(uint32_t tmem_d, const uint8_t* a, const uint8_t* b, bool accumulate) {
   const uint32_t idesc = make_idesc_bf16(128, ND, false, true);
-  const uint32_t aa = smem_u32(a), bb = smem_u32(b);
+  const uint32_t aa = desc_lo(smem_u32(a), 0), bb = desc_lo(smem_u32(b), 16384);
 #pragma unroll
   for (int kb = 0; kb < 2; ++kb)
 #pragma unroll
     for (int k = 0; k < 4; ++k)
-      umma_bf16<1>(tmem_d, make_sw128_desc(aa + kb * 16384 + k * 32, 0, 1024),
-                   make_sw128_desc(bb + kb * 8192 + k * 2048, 16384, 1024), idesc,
+      e_umma_bf16(tmem_d, desc_at(aa, kb * 16384 + k * 32), desc_at(bb, kb * 8192 + k * 2048), idesc,
                    (accumulate || kb != 0 || k != 0) ? 1u : 0u);
 }
 // Row thread `r` writes 8 consecutive values (columns c0 .. c0+7 of its row) of a [128 x 128] bf16 tile in K-major
@@ -198,17 +260,19 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   uint64_t* bar_v = bar_q + 3;  // [2]
   uint64_t* bar_s = bar_q + 5;  // [2]
   uint64_t* bar_o = bar_q + 7;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_q + 8);
+  uint64_t* bar_done = bar_q + 8;  // [2]: all 256 row threads are through with S buffer b (and, in pass 1, wrote P)
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_q + 10);
   float* stat = reinterpret_cast<float*>(smem + L::STAT_OFF);
   uint8_t* blk_ok = smem + L::FLAG_OFF;
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;  // warp-uniform for the compiler
   // the query blocks that see the most keys start first, so the short ones fill the tail of the grid
   const int qb = static_cast<int>(gridDim.x) - 1 - static_cast<int>(blockIdx.x);
   const int bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
   const int row0 = b * p.T + qb * QB;  // first row of this block in the [batch * T] matrices
   const int col0 = h * DH;
-  const bool issuer = (warp == kIssuerWarp && lane == 0);
+  const bool issue_warp = (warp == kIssuerWarp);  // runs the issuing code in lockstep (the e_* instructions elect a lane)
+  const bool issuer = issue_warp && lane == 0;    // one-time set-up only
   const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
 
   if (issuer) {
@@ -216,6 +280,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     tma_prefetch_desc(&tmK);
     tma_prefetch_desc(&tmV);
     for (int i = 0; i < 8; ++i) mbar_init(bar_q + i, 1);
+    mbar_init(&bar_done[0], kRowThreads);
+    mbar_init(&bar_done[1], kRowThreads);
     fence_mbar_init();
   }
   if (warp == kIssuerWarp) {
@@ -227,36 +293,37 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_s = *tmem_slot, tmem_o = tmem_s + 256;  // S buffers at +0 and +128
+  const uint32_t tmem_s = __shfl_sync(0xffffffffu, *tmem_slot, 0), tmem_o = tmem_s + 256;  // S buffers at +0 and +128
 
   int j_lo, j_hi;
   kv_range(qb, p.window, j_lo, j_hi);
   const int nj = j_hi - j_lo + 1, n_tiles = 2 * nj;
+  // (the lambdas below are called by the whole, converged issuing warp: the e_* instructions elect their own lane)
   auto load_k = [&](int t) {  // K block of tile t -> K buffer t & 1
     const int bi = t & 1, u = t >= nj ? t - nj : t;
-    mbar_arrive_expect_tx(&bar_k[bi], L::TILE);
+    e_arrive_expect_tx(&bar_k[bi], L::TILE);
     load_tile<DH>(sK + bi * L::TILE, &tmK, &bar_k[bi], b * p.T + (j_lo + u) * QB, col0);
   };
   auto load_v = [&](int u) {  // V block of pass-1 tile u -> V buffer u & 1
     const int bi = u & 1;
-    mbar_arrive_expect_tx(&bar_v[bi], L::TILE);
+    e_arrive_expect_tx(&bar_v[bi], L::TILE);
     load_tile<DH>(sV + bi * L::TILE, &tmV, &bar_v[bi], b * p.T + (j_lo + u) * QB, col0);
   };
   auto issue_s = [&](int t) {  // S(t) = Q.K(t)^T into S buffer t & 1
     const int bi = t & 1;
-    mbar_wait(&bar_k[bi], (t >> 1) & 1);
+    mbar_wait_poll(&bar_k[bi], (t >> 1) & 1);
     tc_fence_after();
     mma_kk<DH>(tmem_s + bi * 128, sQ, sK + bi * L::TILE, 128, false);
-    umma_commit<1>(&bar_s[bi]);
+    e_umma_commit(&bar_s[bi]);
   };
-  if (issuer) {
-    mbar_arrive_expect_tx(bar_q, L::TILE);
+  if (issue_warp) {
+    e_arrive_expect_tx(bar_q, L::TILE);
     load_tile<DH>(sQ, &tmQ, bar_q, row0, col0);
     load_k(0);
     load_k(1);  // n_tiles >= 2
     load_v(0);
     if (nj > 1) load_v(1);
-    mbar_wait(bar_q, 0);
+    mbar_wait_poll(bar_q, 0);
     issue_s(0);
   }
 
@@ -268,15 +335,31 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   float m2 = 0.f, l = 0.f;             // pass 1: the row's maximum in the exp2 domain (0 if it sees no key), partial sum
   bool row_empty = false;
 
-  for (int t = 0; t < n_tiles; ++t) {
-    const int pass = t >= nj, u = pass ? t - nj : t, j = j_lo + u, bi = t & 1;
-    const uint32_t par = (t >> 1) & 1;
-    if (issuer) {
-      mbar_wait(&bar_s[bi], par);           // S(t) is complete: its K buffer is free
+  // No block-wide barrier inside the loop: the row threads report each tile on bar_done and move on, so the eight
+  // warps drift apart by up to a tile and one warp's TMEM-load / MUFU latencies hide behind another's arithmetic.
+  if (issue_warp) {
+    for (int t = 0; t < n_tiles; ++t) {
+      const int pass = t >= nj, u = pass ? t - nj : t, bi = t & 1;
+      mbar_wait_poll(&bar_s[bi], (t >> 1) & 1);  // S(t) is complete: its K buffer is free
       if (t + 2 < n_tiles) load_k(t + 2);
-      if (t + 1 < n_tiles) issue_s(t + 1);  // S buffer (t+1) & 1 was last read for tile t-1, before that tile's sync
-    } else if (warp < kIssuerWarp) {
-      mbar_wait_poll(&bar_s[bi], par);
+      if (t + 1 < n_tiles) {
+        if (t >= 1) mbar_wait_poll(&bar_done[(t + 1) & 1], ((t - 1) >> 1) & 1);  // tile t-1 has left that S buffer
+        issue_s(t + 1);
+      }
+      if (pass) {
+        mbar_wait_poll(&bar_done[bi], (t >> 1) & 1);  // P(u) is in shared memory
+        if (u > 0) mbar_wait_poll(bar_o, (u - 1) & 1);  // (complete: the row threads waited for it) V buffer (u+1) & 1 is free
+        if (u >= 1 && u + 1 < nj) load_v(u + 1);
+        mbar_wait_poll(&bar_v[u & 1], (u >> 1) & 1);
+        tc_fence_after();
+        mma_k_mn<DH>(tmem_o, sP, sV + (u & 1) * L::TILE, u != 0);  // first tile of pass 1 overwrites
+        e_umma_commit(bar_o);
+      }
+    }
+  } else {
+    for (int t = 0; t < n_tiles; ++t) {
+      const int pass = t >= nj, u = pass ? t - nj : t, j = j_lo + u, bi = t & 1;
+      mbar_wait_poll(&bar_s[bi], (t >> 1) & 1);
       tc_fence_after();
       const uint8_t* mr = (mrow != nullptr && !blk_ok[j]) ? mrow : nullptr;
       const bool all_vis = tile_all_visible(qb, j, p.window, mr);
@@ -296,7 +379,15 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
           c1 = fmaxf(c1, fmaxf(v[e + 2], v[e + 3]));
         }
         m_raw = fmaxf(m_raw, fmaxf(c0, c1));
-        if (t == nj - 1) stat[threadIdx.x] = m_raw;
+        tc_fence_before();
+        mbar_arrive(&bar_done[bi]);
+        if (t == nj - 1) {  // end of pass 0: the row's maximum from its two halves
+          stat[threadIdx.x] = m_raw;
+          named_bar_sync(1, kRowThreads);
+          const float mm = fmaxf(stat[r], stat[r + 128]);
+          row_empty = (mm == -INFINITY);  // a row that sees no key: every p becomes exp2(-inf - 0) = 0
+          m2 = row_empty ? 0.f : mm * sl2;
+        }
       } else {
         uint32_t w[32];
         float l0 = 0.f, l1 = 0.f;
@@ -312,31 +403,16 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
 #pragma unroll
         for (int q8 = 0; q8 < 8; ++q8) put8_kmajor(sP, r, half * 64 + q8 * 8, &w[q8 * 4]);
         fence_async_shared();  // P was written through the generic proxy; the MMA reads it through the async one
+        tc_fence_before();
+        mbar_arrive(&bar_done[bi]);
       }
     }
-    tc_fence_before();
-    __syncthreads();
-    if (t == nj - 1 && warp < kIssuerWarp) {  // end of pass 0: the row's maximum from its two halves
-      const float mm = fmaxf(stat[r], stat[r + 128]);
-      row_empty = (mm == -INFINITY);  // a row that sees no key: every p becomes exp2(-inf - 0) = 0
-      m2 = row_empty ? 0.f : mm * sl2;
-    }
-    if (pass && issuer) {
-      if (u > 0) mbar_wait(bar_o, (u - 1) & 1);  // (already complete: the row threads waited for it) V buffer (u+1) & 1 is free
-      if (u >= 1 && u + 1 < nj) load_v(u + 1);
-      mbar_wait(&bar_v[u & 1], (u >> 1) & 1);
-      tc_fence_after();
-      mma_k_mn<DH>(tmem_o, sP, sV + (u & 1) * L::TILE, u != 0);  // first tile of pass 1 overwrites
-      umma_commit<1>(bar_o);
-    }
-  }
-
-  if (warp < kIssuerWarp) {
-    stat[threadIdx.x] = l;  // (the maxima were read a whole pass ago)
+    named_bar_sync(1, kRowThreads);  // every thread has read the maxima (a pass ago, but nothing else orders it)
+    stat[threadIdx.x] = l;
     mbar_wait_poll(bar_o, (nj - 1) & 1);  // the last P.V: O is complete
     tc_fence_after();
+    named_bar_sync(1, kRowThreads);
   }
-  __syncthreads();
   if (warp < kIssuerWarp) {  // O row / sum -> bf16 -> [batch * T, heads * DH]
     const float lsum = stat[r] + stat[r + 128];
     const float inv = lsum > 0.f ? 1.f / lsum : 0.f;
@@ -365,10 +441,13 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
 }
 
 // ------------------------------------------------------------------------------------------------ backward
-// delta[b, h, t] = sum_c dO[row, h * DH + c] * O[row, h * DH + c]: one thread per (row, head).
+// stats[b, h, t] = (lse * log2(e), delta) with delta = sum_c dO[row, h * DH + c] * O[row, h * DH + c]: what the two
+// backward kernels need per query, packed so that one 512-byte bulk copy brings a sub-tile's 64 pairs.
+// One thread per (row, head).
 template <int DH>
 __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __restrict__ o,
-                                                         const __nv_bfloat16* __restrict__ d_o, float* __restrict__ delta,
+                                                         const __nv_bfloat16* __restrict__ d_o,
+                                                         const float* __restrict__ lse, float2* __restrict__ stats,
                                                          int n_rows, int T, int H) {
   const int idx = blockIdx.x * 256 + threadIdx.x;
   if (idx >= n_rows * H) return;
@@ -388,7 +467,8 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
     }
   }
   const int bb = row / T, t = row - bb * T;
-  delta[(static_cast<size_t>(bb) * H + h) * T + t] = acc;
+  const size_t i = (static_cast<size_t>(bb) * H + h) * T + t;
+  stats[i] = make_float2(lse[i] * kLog2e, acc);  // +inf for a row that saw no key: every p is 0
 }
 
 // The backward kernels work on 64-wide sub-tiles of the streamed operand so that everything can be double-buffered
@@ -401,31 +481,30 @@ constexpr int SB = 64;  // rows of a streamed sub-tile
 template <int DH>
 __device__ __forceinline__ void load_sub(uint8_t* dst, const CUtensorMap* tm, uint64_t* bar, int row0, int col0) {
 #pragma unroll
-  for (int kk = 0; kk < DH / 64; ++kk) tma_load_2d(dst + kk * 8192, tm, bar, col0 + kk * 64, row0);
+  for (int kk = 0; kk < DH / 64; ++kk) e_tma_load_2d(dst + kk * 8192, tm, bar, col0 + kk * 64, row0);
 }
 // D[128 x 64] = A.B^T: A a [128 x KD] K-major tile (64-column halves 16 KB apart), B a [64 x KD] K-major sub-tile
 // (halves 8 KB apart).
 template <int KD>
 __device__ __forceinline__ void mma_full_sub(uint32_t tmem_d, const uint8_t* a, const uint8_t* b) {
   const uint32_t idesc = make_idesc_bf16(128, SB, false, false);
-  const uint32_t aa = smem_u32(a), bb = smem_u32(b);
+  const uint32_t aa = desc_lo(smem_u32(a), 0), bb = desc_lo(smem_u32(b), 0);
 #pragma unroll
   for (int kk = 0; kk < KD / 64; ++kk)
 #pragma unroll
     for (int k = 0; k < 4; ++k)
-      umma_bf16<1>(tmem_d, make_sw128_desc(aa + kk * 16384 + k * 32, 0, 1024), make_sw128_desc(bb + kk * 8192 + k * 32, 0, 1024),
-                   idesc, (kk != 0 || k != 0) ? 1u : 0u);
+      e_umma_bf16(tmem_d, desc_at(aa, kk * 16384 + k * 32), desc_at(bb, kk * 8192 + k * 32), idesc,
+                   (kk != 0 || k != 0) ? 1u : 0u);
 }
 // D[128 x ND] (+)= A.B: A a [128 x 64] K-major tile the row threads wrote (one 128-byte line per row), B a TMA-loaded
 // [64 K rows x ND] sub-tile in its MN-major view (16 K rows are 2 KB apart, the 64-column halves 8 KB).
 template <int ND>
 __device__ __forceinline__ void mma_k64_mn(uint32_t tmem_d, const uint8_t* a, const uint8_t* b, bool accumulate) {
   const uint32_t idesc = make_idesc_bf16(128, ND, false, true);
-  const uint32_t aa = smem_u32(a), bb = smem_u32(b);
+  const uint32_t aa = desc_lo(smem_u32(a), 0), bb = desc_lo(smem_u32(b), 8192);
 #pragma unroll
   for (int k = 0; k < 4; ++k)
-    umma_bf16<1>(tmem_d, make_sw128_desc(aa + k * 32, 0, 1024), make_sw128_desc(bb + k * 2048, 8192, 1024), idesc,
-                 (accumulate || k != 0) ? 1u : 0u);
+    e_umma_bf16(tmem_d, desc_at(aa, k * 32), desc_at(bb, k * 2048), idesc, (accumulate || k != 0) ? 1u : 0u);
 }
 // Row `r` of a [128 x 64] K-major tile: 8 consecutive bf16 values at columns c0 .. c0 + 7 (c0 < 64).
 __device__ __forceinline__ void put8_row64(uint8_t* tile, int r, int c0, const uint32_t w[4]) {
@@ -468,8 +547,8 @@ struct BwdKvSmem {
   // stationary K and V, a three-stage ring of (Q_i, dO_i) sub-tiles, two buffers each of the P^T and dS^T tiles
   static constexpr uint32_t K_OFF = 0, V_OFF = TILE, Q_OFF = 2 * TILE, DO_OFF = Q_OFF + 3 * SUB, PT_OFF = DO_OFF + 3 * SUB,
                             DST_OFF = PT_OFF + 2 * 16384, BAR_OFF = DST_OFF + 2 * 16384;
-  static constexpr uint32_t STAT_OFF = BAR_OFF + 128;  // [2][64] (log2-sum-exp, delta) of the queries of a sub-tile
-  static constexpr uint32_t BYTES = 1024 + STAT_OFF + 2 * SB * 8;
+  static constexpr uint32_t STAT_OFF = BAR_OFF + 128;  // [3][64] (log2-sum-exp, delta) of the queries of a sub-tile
+  static constexpr uint32_t BYTES = 1024 + STAT_OFF + 3 * SB * 8;
   static_assert(BYTES <= 232448, "exceeds the 227 KB of shared memory a CTA can have");
 };
 
@@ -495,19 +574,23 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   uint64_t* bar_qd = bar_kv + 1;  // [3]
   uint64_t* bar_s = bar_kv + 4;   // [2]
   uint64_t* bar_o = bar_kv + 6;   // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_kv + 8);
-  float2* stat = reinterpret_cast<float2*>(smem + L::STAT_OFF);  // [2][64]
+  uint64_t* bar_done = bar_kv + 8;  // [2]: all 256 row threads have written P^T / dS^T of buffer b
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_kv + 10);
+  float2* stat = reinterpret_cast<float2*>(smem + L::STAT_OFF);  // [3][64], filled by TMA with the (Q_i, dO_i) stage
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;  // warp-uniform for the compiler
   const int kb = blockIdx.x, bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;  // key block 0 sees the most queries
   const int col0 = h * DH;
-  const bool issuer = (warp == kIssuerWarp && lane == 0);
+  const bool issue_warp = (warp == kIssuerWarp);  // runs the issuing code in lockstep (the e_* instructions elect a lane)
+  const bool issuer = issue_warp && lane == 0;    // one-time set-up only
   if (issuer) {
     tma_prefetch_desc(&tmQ);
     tma_prefetch_desc(&tmK);
     tma_prefetch_desc(&tmV);
     tma_prefetch_desc(&tmDO);
     for (int i = 0; i < 8; ++i) mbar_init(bar_kv + i, 1);
+    mbar_init(&bar_done[0], kRowThreads);
+    mbar_init(&bar_done[1], kRowThreads);
     fence_mbar_init();
   }
   // query sub-blocks that see this key block
@@ -515,49 +598,38 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   int last_q = p.T - 1;
   if (p.window > 0) last_q = min(last_q, kb * QB + QB - 1 + p.window - 1);
   const int n = last_q / SB - is_lo + 1;
-  const size_t stat0 = static_cast<size_t>(bh) * p.T + static_cast<size_t>(is_lo) * SB;  // index of the first query's lse
-  auto load_stats = [&](int t) {  // threads 0-63: log2-sum-exp, 64-127: delta of the 64 queries of sub-tile t
-    if (threadIdx.x < 2 * SB && t < n) {
-      const int q = threadIdx.x & (SB - 1);
-      float* dst = reinterpret_cast<float*>(&stat[(t & 1) * SB + q]);
-      if (threadIdx.x < SB)
-        dst[0] = p.lse[stat0 + t * SB + q] * kLog2e;  // +inf for a row that saw no key: every p is 0
-      else
-        dst[1] = p.delta[stat0 + t * SB + q];
-    }
-  };
+  const float2* gstat = p.stats + static_cast<size_t>(bh) * p.T + static_cast<size_t>(is_lo) * SB;
   if (warp == kIssuerWarp) {
     tmem_alloc<1>(tmem_slot, 512);
     tmem_relinquish<1>();
-  } else {
-    load_stats(0);
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot, tmem_dv = tmem_base + 256, tmem_dk = tmem_base + 384;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0), tmem_dv = tmem_base + 256, tmem_dk = tmem_base + 384;
 
   auto load_qd = [&](int t) {  // (Q_i, dO_i) of sub-tile t -> ring stage t % 3
     const int st = t % 3, row = b * p.T + (is_lo + t) * SB;
-    mbar_arrive_expect_tx(&bar_qd[st], 2 * L::SUB);
+    e_arrive_expect_tx(&bar_qd[st], 2 * L::SUB + SB * 8);
     load_sub<DH>(sQ + st * L::SUB, &tmQ, &bar_qd[st], row, col0);
     load_sub<DH>(sDO + st * L::SUB, &tmDO, &bar_qd[st], row, col0);
+    e_bulk_load_1d(stat + st * SB, gstat + t * SB, SB * 8, &bar_qd[st]);  // the 64 queries' (log2-sum-exp, delta)
   };
   auto issue_s = [&](int t) {  // S^T(t) and dP^T(t) into TMEM buffer t & 1
     const int st = t % 3;
-    mbar_wait(&bar_qd[st], (t / 3) & 1);
+    mbar_wait_poll(&bar_qd[st], (t / 3) & 1);
     tc_fence_after();
     mma_full_sub<DH>(tmem_base + (t & 1) * 128, sK, sQ + st * L::SUB);
     mma_full_sub<DH>(tmem_base + (t & 1) * 128 + SB, sV, sDO + st * L::SUB);
-    umma_commit<1>(&bar_s[t & 1]);
+    e_umma_commit(&bar_s[t & 1]);
   };
-  if (issuer) {
-    mbar_arrive_expect_tx(bar_kv, 2 * L::TILE);
+  if (issue_warp) {  // (the lambdas are called by the whole, converged issuing warp: the e_* instructions elect their own lane)
+    e_arrive_expect_tx(bar_kv, 2 * L::TILE);
     load_tile<DH>(sK, &tmK, bar_kv, b * p.T + kb * QB, col0);
     load_tile<DH>(sV, &tmV, bar_kv, b * p.T + kb * QB, col0);
     load_qd(0);
     if (n > 1) load_qd(1);
-    mbar_wait(bar_kv, 0);
+    mbar_wait_poll(bar_kv, 0);
     issue_s(0);
   }
 
@@ -568,15 +640,26 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   bool key_ok = true;  // a padded key is never attended: its whole row of P is 0
   if (warp < kIssuerWarp && p.key_mask != nullptr) key_ok = p.key_mask[static_cast<size_t>(b) * p.T + kj] != 0;
 
-  for (int t = 0; t < n; ++t) {
-    const int sb = t & 1, st = t % 3;
-    if (issuer) {
-      mbar_wait(&bar_s[sb], (t >> 1) & 1);
-      if (t >= 1) mbar_wait(&bar_o[(t - 1) & 1], ((t - 1) >> 1) & 1);  // ring stage (t + 2) % 3 is free again
-      if (t + 2 < n) load_qd(t + 2);
-      if (t + 1 < n) issue_s(t + 1);  // TMEM buffer (t + 1) & 1 was last read for sub-tile t - 1, before its sync
-    } else if (warp < kIssuerWarp) {
+  // No block-wide barrier inside the loop (see the forward kernel): the row threads report on bar_done and move on.
+  if (issue_warp) {
+    for (int t = 0; t < n; ++t) {
+      const int sb = t & 1, st = t % 3;
       mbar_wait_poll(&bar_s[sb], (t >> 1) & 1);
+      if (t >= 1) mbar_wait_poll(&bar_o[(t - 1) & 1], ((t - 1) >> 1) & 1);  // ring stage (t + 2) % 3 is free again
+      if (t + 2 < n) load_qd(t + 2);
+      // TMEM buffer (t + 1) & 1 was last read for sub-tile t - 1, whose bar_done was awaited an iteration ago
+      if (t + 1 < n) issue_s(t + 1);
+      mbar_wait_poll(&bar_done[sb], (t >> 1) & 1);  // P^T(t) and dS^T(t) are in shared memory
+      tc_fence_after();
+      mma_k64_mn<DH>(tmem_dv, sPT + sb * 16384, sDO + st * L::SUB, t != 0);  // dV += P^T . dO_i
+      mma_k64_mn<DH>(tmem_dk, sDST + sb * 16384, sQ + st * L::SUB, t != 0);  // dK += dS^T . Q_i
+      e_umma_commit(&bar_o[sb]);
+    }
+  } else {
+    for (int t = 0; t < n; ++t) {
+      const int sb = t & 1, st = t % 3;
+      mbar_wait_poll(&bar_s[sb], (t >> 1) & 1);
+      mbar_wait_poll(&bar_qd[st], (t / 3) & 1);  // (complete) acquire of this stage's TMA writes: the queries' statistics
       tc_fence_after();
       float v[32], g[32];
       tmem_ld32(tmem_base + sb * 128 + lane_off + half * 32, v);
@@ -586,7 +669,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       // every query of the sub-tile sees every key of the block?  (then only the padding flag of the key matters)
       const bool all_vis = (is_lo + t) * SB >= kb * QB + QB - 1 &&
                            (p.window <= 0 || (is_lo + t) * SB + SB - 1 - p.window < kb * QB);
-      const float2* sq = stat + sb * SB + half * 32;
+      const float2* sq = stat + st * SB + half * 32;
       // queries q0 + c that see key kj: q >= kj, and q < kj + window for a sliding window; none if the key is padding
       uint32_t bits = 0xffffffffu;
       if (!all_vis) bits = range_bits(kj - q0, p.window > 0 ? kj + p.window - 1 - q0 : 31);
@@ -610,15 +693,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         put8_row64(dst, r, half * 32 + q8 * 8, &wd[q8 * 4]);
       }
       fence_async_shared();
-      load_stats(t + 1);  // its buffer was last read for sub-tile t - 1
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (issuer) {
-      tc_fence_after();
-      mma_k64_mn<DH>(tmem_dv, sPT + sb * 16384, sDO + st * L::SUB, t != 0);  // dV += P^T . dO_i
-      mma_k64_mn<DH>(tmem_dk, sDST + sb * 16384, sQ + st * L::SUB, t != 0);  // dK += dS^T . Q_i
-      umma_commit<1>(&bar_o[sb]);
+      tc_fence_before();
+      mbar_arrive(&bar_done[sb]);
     }
   }
 
@@ -666,14 +742,16 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   uint64_t* bar_kv = bar_q + 1;  // [3]
   uint64_t* bar_s = bar_q + 4;   // [2]
   uint64_t* bar_o = bar_q + 6;   // [2]
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_q + 8);
+  uint64_t* bar_done = bar_q + 8;  // [2]: all 256 row threads have written dS of buffer b
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar_q + 10);
   uint8_t* sub_ok = smem + L::FLAG_OFF;
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;  // warp-uniform for the compiler
   const int qb = static_cast<int>(gridDim.x) - 1 - static_cast<int>(blockIdx.x);  // longest key ranges first
   const int bh = blockIdx.y, b = bh / p.H, h = bh - b * p.H;
   const int col0 = h * DH;
-  const bool issuer = (warp == kIssuerWarp && lane == 0);
+  const bool issue_warp = (warp == kIssuerWarp);  // runs the issuing code in lockstep (the e_* instructions elect a lane)
+  const bool issuer = issue_warp && lane == 0;    // one-time set-up only
   const uint8_t* mrow = p.key_mask != nullptr ? p.key_mask + static_cast<size_t>(b) * p.T : nullptr;
   if (issuer) {
     tma_prefetch_desc(&tmQ);
@@ -681,6 +759,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     tma_prefetch_desc(&tmV);
     tma_prefetch_desc(&tmDO);
     for (int i = 0; i < 8; ++i) mbar_init(bar_q + i, 1);
+    mbar_init(&bar_done[0], kRowThreads);
+    mbar_init(&bar_done[1], kRowThreads);
     fence_mbar_init();
   }
   if (warp == kIssuerWarp) {
@@ -692,7 +772,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
-  const uint32_t tmem_base = *tmem_slot, tmem_dq = tmem_base + 256;
+  const uint32_t tmem_base = __shfl_sync(0xffffffffu, *tmem_slot, 0), tmem_dq = tmem_base + 256;
 
   // key sub-blocks this query block sees
   int first_key = 0;
@@ -700,25 +780,25 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   const int js_lo = first_key / SB, n = 2 * qb + 1 - js_lo + 1;
   auto load_kv = [&](int t) {  // (K_j, V_j) of sub-tile t -> ring stage t % 3
     const int st = t % 3, row = b * p.T + (js_lo + t) * SB;
-    mbar_arrive_expect_tx(&bar_kv[st], 2 * L::SUB);
+    e_arrive_expect_tx(&bar_kv[st], 2 * L::SUB);
     load_sub<DH>(sK + st * L::SUB, &tmK, &bar_kv[st], row, col0);
     load_sub<DH>(sV + st * L::SUB, &tmV, &bar_kv[st], row, col0);
   };
   auto issue_s = [&](int t) {  // S(t) = Q.K_j^T and dP(t) = dO.V_j^T into TMEM buffer t & 1
     const int st = t % 3;
-    mbar_wait(&bar_kv[st], (t / 3) & 1);
+    mbar_wait_poll(&bar_kv[st], (t / 3) & 1);
     tc_fence_after();
     mma_full_sub<DH>(tmem_base + (t & 1) * 128, sQ, sK + st * L::SUB);
     mma_full_sub<DH>(tmem_base + (t & 1) * 128 + SB, sDO, sV + st * L::SUB);
-    umma_commit<1>(&bar_s[t & 1]);
+    e_umma_commit(&bar_s[t & 1]);
   };
-  if (issuer) {
-    mbar_arrive_expect_tx(bar_q, 2 * L::TILE);
+  if (issue_warp) {  // (the lambdas are called by the whole, converged issuing warp: the e_* instructions elect their own lane)
+    e_arrive_expect_tx(bar_q, 2 * L::TILE);
     load_tile<DH>(sQ, &tmQ, bar_q, b * p.T + qb * QB, col0);
     load_tile<DH>(sDO, &tmDO, bar_q, b * p.T + qb * QB, col0);
     load_kv(0);
     if (n > 1) load_kv(1);
-    mbar_wait(bar_q, 0);
+    mbar_wait_poll(bar_q, 0);
     issue_s(0);
   }
 
@@ -727,19 +807,26 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   const float sl2 = p.scale * kLog2e;
   float lse2 = 0.f, dl = 0.f;
   if (warp < kIssuerWarp) {
-    const size_t sidx = static_cast<size_t>(bh) * p.T + qi;
-    lse2 = p.lse[sidx] * kLog2e;  // +inf for a row that saw no key: every p is 0
-    dl = p.delta[sidx];
+    const float2 sd = p.stats[static_cast<size_t>(bh) * p.T + qi];
+    lse2 = sd.x;  // +inf for a row that saw no key: every p is 0
+    dl = sd.y;
   }
 
-  for (int t = 0; t < n; ++t) {
-    const int sb = t & 1, st = t % 3, js = js_lo + t;
-    if (issuer) {
-      mbar_wait(&bar_s[sb], (t >> 1) & 1);
-      if (t >= 1) mbar_wait(&bar_o[(t - 1) & 1], ((t - 1) >> 1) & 1);  // ring stage (t + 2) % 3 is free again
+  if (issue_warp) {
+    for (int t = 0; t < n; ++t) {
+      const int sb = t & 1, st = t % 3;
+      mbar_wait_poll(&bar_s[sb], (t >> 1) & 1);
+      if (t >= 1) mbar_wait_poll(&bar_o[(t - 1) & 1], ((t - 1) >> 1) & 1);  // ring stage (t + 2) % 3 is free again
       if (t + 2 < n) load_kv(t + 2);
-      if (t + 1 < n) issue_s(t + 1);
-    } else if (warp < kIssuerWarp) {
+      if (t + 1 < n) issue_s(t + 1);  // its TMEM buffer was last read for sub-tile t - 1 (bar_done awaited then)
+      mbar_wait_poll(&bar_done[sb], (t >> 1) & 1);  // dS(t) is in shared memory
+      tc_fence_after();
+      mma_k64_mn<DH>(tmem_dq, sDS + sb * 16384, sK + st * L::SUB, t != 0);  // dQ += dS . K_j
+      e_umma_commit(&bar_o[sb]);
+    }
+  } else {
+    for (int t = 0; t < n; ++t) {
+      const int sb = t & 1, js = js_lo + t;
       mbar_wait_poll(&bar_s[sb], (t >> 1) & 1);
       tc_fence_after();
       float v[32], g[32];
@@ -762,13 +849,8 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
 #pragma unroll
       for (int q8 = 0; q8 < 4; ++q8) put8_row64(ds, r, half * 32 + q8 * 8, &wd[q8 * 4]);
       fence_async_shared();
-    }
-    tc_fence_before();
-    __syncthreads();
-    if (issuer) {
-      tc_fence_after();
-      mma_k64_mn<DH>(tmem_dq, sDS + sb * 16384, sK + st * L::SUB, t != 0);  // dQ += dS . K_j
-      umma_commit<1>(&bar_o[sb]);
+      tc_fence_before();
+      mbar_arrive(&bar_done[sb]);
     }
   }
 
@@ -828,7 +910,7 @@ int run_attn_fwd(const void* q, const void* k, const void* v, const AttnParams& 
 
 template <int DH>
 int run_attn_bwd(const void* q, const void* k, const void* v, const void* o, const void* d_o, AttnParams p, int B,
-                 float* delta, void* dq, void* dk, void* dv, cudaStream_t st) {
+                 float2* stats, void* dq, void* dk, void* dv, cudaStream_t st) {
   CUtensorMap tq, tk, tv, tdo;
   if (int rc = attn_tmap(&tq, q, B, p.T, p.H, DH)) return rc;
   if (int rc = attn_tmap(&tk, k, B, p.T, p.H, DH)) return rc;
@@ -839,9 +921,10 @@ int run_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
   ftk::TimelineScope tl_(FTK_TL_ATTN_BWD, st);
   const int n = B * p.T * p.H;
   attn_delta_kernel<DH><<<(n + 255) / 256, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(o),
-                                                        static_cast<const __nv_bfloat16*>(d_o), delta, B * p.T, p.T, p.H);
+                                                        static_cast<const __nv_bfloat16*>(d_o), p.lse, stats, B * p.T, p.T,
+                                                        p.H);
   FTK_CUDA_CHECK(cudaGetLastError());
-  p.delta = delta;
+  p.stats = stats;
   const dim3 grid(p.T / QB, B * p.H);
   p.out0 = static_cast<__nv_bfloat16*>(dk);
   p.out1 = static_cast<__nv_bfloat16*>(dv);
@@ -877,7 +960,7 @@ extern "C" int ftk_attention_fwd(const void* Q, const void* K, const void* V, co
 
 extern "C" size_t ftk_attention_bwd_workspace(int32_t B, int32_t T, int32_t H) {
   if (B <= 0 || T <= 0 || H <= 0) return 0;
-  return static_cast<size_t>(B) * T * H * sizeof(float);
+  return static_cast<size_t>(B) * T * H * sizeof(float2);  // (lse * log2(e), rowsum(dO * O)) per query and head
 }
 
 extern "C" int ftk_attention_bwd(const void* Q, const void* K, const void* V, const void* O, const void* dO,
@@ -899,7 +982,8 @@ extern "C" int ftk_attention_bwd(const void* Q, const void* K, const void* V, co
   p.window = window;
   p.scale = scale;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  float* delta = static_cast<float*>(workspace);
-  return head_dim == 128 ? run_attn_bwd<128>(Q, K, V, O, dO, p, B, delta, dQ, dK, dV, st)
-                         : run_attn_bwd<64>(Q, K, V, O, dO, p, B, delta, dQ, dK, dV, st);
+  FTK_REQUIRE(reinterpret_cast<uintptr_t>(workspace) % 16 == 0, "ftk_attention_bwd: workspace must be 16-byte aligned");
+  float2* stats = static_cast<float2*>(workspace);
+  return head_dim == 128 ? run_attn_bwd<128>(Q, K, V, O, dO, p, B, stats, dQ, dK, dV, st)
+                         : run_attn_bwd<64>(Q, K, V, O, dO, p, B, stats, dQ, dK, dV, st);
 }
