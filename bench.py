@@ -620,8 +620,9 @@ def main_gpu(args) -> None:
 def run_full_step(dev) -> dict:
     """Context for the headline: one whole finetune step of GPT-Neo-1.3B (BASELINE configs[2]: ctx 2048, batch 8, bf16,
     gradient checkpointing as the reference enables it, torch fused AdamW) on this GPU, with HF's eager blocks + HF's
-    lm_head/loss, and with this package's fused loss + trunk kernels (patch_gpt_neo).  tokens/s/GPU of the metric's
-    first half.  Errors are reported, not raised: this block must not take the bench line down."""
+    lm_head/loss, with this package's fused loss + trunk kernels (patch_gpt_neo), and the latter once more with
+    gradient checkpointing off (same arithmetic; 180 GB of HBM hold what the reference's 48 GB cards had to
+    recompute).  tokens/s/GPU of the metric's first half.  Errors are reported, not raised: this block must not take the bench line down."""
     import torch
     try:
         from kubernetes_cloud_b200 import trunk
@@ -649,9 +650,13 @@ def run_full_step(dev) -> dict:
 
         out = {"model": "GPT-Neo-1.3B, ctx 2048, batch 8, bf16, gradient checkpointing, torch fused AdamW",
                "tokens_per_step": B * T}
-        for name, ours, n in (("hf_eager", False, 2), ("ftk_loss_and_trunk", True, 5)):
-            if ours:
+        for name, ours, n in (("hf_eager", False, 2), ("ftk_loss_and_trunk", True, 5),
+                              ("ftk_loss_and_trunk_no_recompute", True, 5)):
+            if name == "ftk_loss_and_trunk":
                 out["modules_rebound"] = trunk.patch_gpt_neo(model)
+            if name.endswith("no_recompute"):  # same arithmetic, activations kept in HBM instead of a second forward
+                model.gradient_checkpointing_disable()
+                torch.cuda.reset_peak_memory_stats(dev)
             for _ in range(2):
                 step(ours)
             torch.cuda.synchronize(dev)
@@ -660,8 +665,11 @@ def run_full_step(dev) -> dict:
                 loss = step(ours)
             torch.cuda.synchronize(dev)
             dt = (time.time() - t0) / n
-            out[name] = {"ms_per_step": dt * 1e3, "tokens_per_s_per_gpu": B * T / dt, "loss": float(loss.detach())}
+            out[name] = {"ms_per_step": dt * 1e3, "tokens_per_s_per_gpu": B * T / dt, "loss": float(loss.detach()),
+                         "peak_mem_gb": torch.cuda.max_memory_allocated(dev) / 1e9}
         out["speedup"] = out["hf_eager"]["ms_per_step"] / out["ftk_loss_and_trunk"]["ms_per_step"]
+        out["speedup_no_recompute"] = (out["hf_eager"]["ms_per_step"] /
+                                       out["ftk_loss_and_trunk_no_recompute"]["ms_per_step"])
         del model, opt
         torch.cuda.empty_cache()
         return out

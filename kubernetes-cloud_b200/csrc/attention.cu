@@ -51,7 +51,7 @@ constexpr int kMaxKeyBlocks = 256;  // per-key-block padding flags kept in share
 struct AttnParams {
   const uint8_t* key_mask;  // [batch * T] (1 = may be attended) or null
   float* lse;               // [batch * heads * T]
-  const float2* stats;      // backward: (lse * log2(e), rowsum(dO * O)) [batch * heads * T]
+  const float2* stats;      // backward: (lse * log2(e), scale * rowsum(dO * O)) [batch * heads * T]
   __nv_bfloat16* out0;      // forward: O; kv kernel: dK; q kernel: dQ     ([batch * T, heads * head_dim])
   __nv_bfloat16* out1;      // kv kernel: dV
   int T, H, window;         // window > 0: key j is visible from query i iff i - window < j <= i; 0: plain causal
@@ -441,14 +441,14 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
 }
 
 // ------------------------------------------------------------------------------------------------ backward
-// stats[b, h, t] = (lse * log2(e), delta) with delta = sum_c dO[row, h * DH + c] * O[row, h * DH + c]: what the two
-// backward kernels need per query, packed so that one 512-byte bulk copy brings a sub-tile's 64 pairs.
-// One thread per (row, head).
+// stats[b, h, t] = (lse * log2(e), scale * delta) with delta = sum_c dO[row, h * DH + c] * O[row, h * DH + c]: what the
+// two backward kernels need per query (dS = P * (scale * dP - scale * delta)), packed so that one 512-byte bulk copy
+// brings a sub-tile's 64 pairs.  One thread per (row, head).
 template <int DH>
 __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __restrict__ o,
                                                          const __nv_bfloat16* __restrict__ d_o,
                                                          const float* __restrict__ lse, float2* __restrict__ stats,
-                                                         int n_rows, int T, int H) {
+                                                         int n_rows, int T, int H, float scale) {
   const int idx = blockIdx.x * 256 + threadIdx.x;
   if (idx >= n_rows * H) return;
   const int row = idx / H, h = idx - row * H;
@@ -468,7 +468,7 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
   }
   const int bb = row / T, t = row - bb * T;
   const size_t i = (static_cast<size_t>(bb) * H + h) * T + t;
-  stats[i] = make_float2(lse[i] * kLog2e, acc);  // +inf for a row that saw no key: every p is 0
+  stats[i] = make_float2(lse[i] * kLog2e, acc * scale);  // lse = +inf for a row that saw no key: every p is 0
 }
 
 // The backward kernels work on 64-wide sub-tiles of the streamed operand so that everything can be double-buffered
@@ -669,20 +669,30 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       // every query of the sub-tile sees every key of the block?  (then only the padding flag of the key matters)
       const bool all_vis = (is_lo + t) * SB >= kb * QB + QB - 1 &&
                            (p.window <= 0 || (is_lo + t) * SB + SB - 1 - p.window < kb * QB);
-      const float2* sq = stat + st * SB + half * 32;
-      // queries q0 + c that see key kj: q >= kj, and q < kj + window for a sliding window; none if the key is padding
-      uint32_t bits = 0xffffffffu;
-      if (!all_vis) bits = range_bits(kj - q0, p.window > 0 ? kj + p.window - 1 - q0 : 31);
-      if (!key_ok) bits = 0u;
+      // (log2-sum-exp, scale * delta) of this thread's 32 queries, two queries per 16-byte broadcast read
+      const float4* sq = reinterpret_cast<const float4*>(stat + st * SB + half * 32);
       uint32_t wp[16], wd[16];
+      if (all_vis && key_ok) {
 #pragma unroll
-      for (int e = 0; e < 16; ++e) {
-        const float2 s0 = sq[2 * e], s1 = sq[2 * e + 1];  // (log2-sum-exp, delta) of the two queries: broadcast reads
-        float p0 = fast_exp2(fmaf(v[2 * e], sl2, -s0.x)), p1 = fast_exp2(fmaf(v[2 * e + 1], sl2, -s1.x));
-        if (!((bits >> (2 * e)) & 1u)) p0 = 0.f;
-        if (!((bits >> (2 * e + 1)) & 1u)) p1 = 0.f;
-        wp[e] = pack2(p0, p1);
-        wd[e] = pack2(p.scale * p0 * (g[2 * e] - s0.y), p.scale * p1 * (g[2 * e + 1] - s1.y));
+        for (int e = 0; e < 16; ++e) {
+          const float4 sd = sq[e];
+          const float p0 = fast_exp2(fmaf(v[2 * e], sl2, -sd.x)), p1 = fast_exp2(fmaf(v[2 * e + 1], sl2, -sd.z));
+          wp[e] = pack2(p0, p1);
+          wd[e] = pack2(p0 * fmaf(g[2 * e], p.scale, -sd.y), p1 * fmaf(g[2 * e + 1], p.scale, -sd.w));
+        }
+      } else {
+        // queries q0 + c that see key kj: q >= kj, and q < kj + window for a sliding window; none if the key is padding
+        uint32_t bits = all_vis ? 0xffffffffu : range_bits(kj - q0, p.window > 0 ? kj + p.window - 1 - q0 : 31);
+        if (!key_ok) bits = 0u;
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          const float4 sd = sq[e];
+          float p0 = fast_exp2(fmaf(v[2 * e], sl2, -sd.x)), p1 = fast_exp2(fmaf(v[2 * e + 1], sl2, -sd.z));
+          if (!((bits >> (2 * e)) & 1u)) p0 = 0.f;
+          if (!((bits >> (2 * e + 1)) & 1u)) p1 = 0.f;
+          wp[e] = pack2(p0, p1);
+          wd[e] = pack2(p0 * fmaf(g[2 * e], p.scale, -sd.y), p1 * fmaf(g[2 * e + 1], p.scale, -sd.w));
+        }
       }
       if (t >= 2) mbar_wait_poll(&bar_o[sb], ((t - 2) >> 1) & 1);  // the MMAs that read these two buffers are done
       uint8_t* pt = sPT + sb * 16384;
@@ -842,7 +852,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
 #pragma unroll
       for (int e = 0; e < 16; ++e) {
         const float p0 = fast_exp2(fmaf(v[2 * e], sl2, -lse2)), p1 = fast_exp2(fmaf(v[2 * e + 1], sl2, -lse2));
-        wd[e] = pack2(p.scale * p0 * (g[2 * e] - dl), p.scale * p1 * (g[2 * e + 1] - dl));
+        wd[e] = pack2(p0 * fmaf(g[2 * e], p.scale, -dl), p1 * fmaf(g[2 * e + 1], p.scale, -dl));  // dl = scale * delta
       }
       if (t >= 2) mbar_wait_poll(&bar_o[sb], ((t - 2) >> 1) & 1);  // the MMA that read this dS buffer is done
       uint8_t* ds = sDS + sb * 16384;
@@ -922,7 +932,7 @@ int run_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
   const int n = B * p.T * p.H;
   attn_delta_kernel<DH><<<(n + 255) / 256, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(o),
                                                         static_cast<const __nv_bfloat16*>(d_o), p.lse, stats, B * p.T, p.T,
-                                                        p.H);
+                                                        p.H, p.scale);
   FTK_CUDA_CHECK(cudaGetLastError());
   p.stats = stats;
   const dim3 grid(p.T / QB, B * p.H);

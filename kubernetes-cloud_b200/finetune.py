@@ -155,6 +155,10 @@ def build_parser() -> DashParser:
     p.add_argument("--max-steps", type=int, default=-1, help="stop after this many optimizer steps")
     p.add_argument("--max-grad-norm", type=float, default=1.0)
     p.add_argument("--report-json", type=str, default="", help="write per-step metrics here")
+    p.add_argument("--ftk-recompute", choices=("auto", "on", "off"), default="auto",
+                   help="gradient checkpointing (FT.py:884, :995: always on in the reference, sized for 48 GB cards). "
+                        "'off' keeps every block's activations for the backward instead of re-running its forward; "
+                        "'auto' does so when they fit in half of the free device memory (180 GB of HBM usually do)")
     p.add_argument("--no-ftk-trunk", action=FuzzyBool, dest="ftk_trunk", default=True,
                    help="keep HF's eager GPT-Neo blocks; by default their MLP, projections and attention run on this "
                         "package's kernels (trunk.patch_gpt_neo) when the context size is a multiple of 128")
@@ -238,7 +242,8 @@ def main(argv: Optional[List[str]] = None) -> dict:
 
     model = load_model(args.model).to(dev).to(torch.bfloat16)
     model.train()  # FT.py:831
-    if hasattr(model, "gradient_checkpointing_enable"):
+    checkpointing = hasattr(model, "gradient_checkpointing_enable")
+    if checkpointing:
         model.gradient_checkpointing_enable()  # FT.py:884
     if (args.ftk_trunk and getattr(model.config, "model_type", "") == "gpt_neo" and model.config.hidden_size % 64 == 0
             and getattr(model.config, "activation_function", "") == "gelu_new"):
@@ -247,7 +252,8 @@ def main(argv: Optional[List[str]] = None) -> dict:
         attn_ok = args.context_size % 128 == 0 and model.config.hidden_size // model.config.num_heads in (64, 128)
         n_mod = trunk.patch_gpt_neo(model, attention_kernels=attn_ok)
         if main_proc:
-            logger.info("TRUNK: %d GPT-Neo modules rebound to the tcgen05 linear / MLP / attention kernels", n_mod)
+            logger.info("TRUNK: %d GPT-Neo modules rebound to this package's linear / MLP / attention / LayerNorm kernels",
+                        n_mod)
     if rep.max_token >= model.config.vocab_size:
         raise SystemExit(f"token id {rep.max_token} does not fit the model's vocabulary {model.config.vocab_size}")
 
@@ -275,6 +281,20 @@ def main(argv: Optional[List[str]] = None) -> dict:
     sync = GradSync(model.parameters(), rank, world)
     opt = FusedAdamW(sync, lr=args.lr, weight_decay=0.01, max_grad_norm=args.max_grad_norm,
                      schedule=WarmupLR(args.lr, max(2, int(float(args.warmup_ratio) * total_steps))))
+    if checkpointing and args.ftk_recompute != "on":
+        # kept per block and token without recomputation: ~16 bf16 [d] rows (LayerNorm inputs, q / k / v / o, the MLP's
+        # input, pre-activation and activation at 4 d each, the residuals)
+        cfg = model.config
+        d_model = getattr(cfg, "hidden_size", getattr(cfg, "n_embd", 2048))
+        n_layer = getattr(cfg, "num_layers", getattr(cfg, "n_layer", getattr(cfg, "num_hidden_layers", 24)))
+        need = bs * args.context_size * n_layer * d_model * 2 * 16
+        free, _total = torch.cuda.mem_get_info(dev)
+        if args.ftk_recompute == "off" or need <= free // 2:
+            model.gradient_checkpointing_disable()
+            checkpointing = False
+    if main_proc:
+        logger.info("RECOMPUTE: gradient checkpointing %s", "on (as the reference)" if checkpointing else
+                    "off (activations kept in HBM)")
 
     history = []
     step = 0

@@ -43,11 +43,17 @@ def step(fused: bool):
 out = {"arch": arch, "batch": B, "ctx": T, "tokens": B * T}
 variants = [("hf_lm_head_and_loss", False), ("fused_lm_head_ce", True)]
 if model.config.model_type == "gpt_neo":
-    variants.append(("fused_lm_head_ce_and_ftk_trunk", True))  # + trunk.patch_gpt_neo: MLP, projections and attention on our kernels
+    # + trunk.patch_gpt_neo: whole blocks (LayerNorm, projections, attention, MLP, residual adds) on our kernels
+    variants.append(("fused_lm_head_ce_and_ftk_trunk", True))
+    # the same without gradient checkpointing: 180 GB of HBM hold the activations the reference's 48 GB cards had to
+    # recompute (FT.py:884); identical arithmetic, one forward pass less
+    variants.append(("fused_lm_head_ce_and_ftk_trunk_no_recompute", True))
 for name, fused in variants:
     if name.endswith("ftk_trunk"):
         from kubernetes_cloud_b200 import trunk
         out["modules_rebound"] = trunk.patch_gpt_neo(model)
+    if name.endswith("no_recompute"):
+        model.gradient_checkpointing_disable()
     torch.cuda.empty_cache()
     torch.cuda.reset_peak_memory_stats()
     for _ in range(2):
