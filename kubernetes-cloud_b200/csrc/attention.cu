@@ -58,6 +58,17 @@ struct AttnParams {
   float scale;              // S = scale * Q.K^T
 };
 
+// Explicit shared-space accesses for the hot loops: the tile pointers are carved out of an aligned-up generic pointer,
+// so plain dereferences compile to generic LD.E / ST.E with 64-bit addresses instead of LDS / STS.
+__device__ __forceinline__ void sts128(uint32_t saddr, const uint32_t w[4]) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(saddr), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]) : "memory");
+}
+__device__ __forceinline__ float4 lds128f(uint32_t saddr) {
+  float4 r;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(r.x), "=f"(r.y), "=f"(r.z), "=f"(r.w) : "r"(saddr));
+  return r;
+}
+
 __device__ __forceinline__ uint32_t pack2(float lo, float hi) {
   __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&h);
@@ -177,9 +188,8 @@ __device__ __forceinline__ void mma_k_mn(uint32_t tmem_d, const uint8_t* a, cons
 // Row thread `r` writes 8 consecutive values (columns c0 .. c0+7 of its row) of a [128 x 128] bf16 tile in K-major
 // form (the tile is an A operand with rows = M): half (c0 / 64) at +16 KB, row r at r * 128 B, 16-byte chunk c at
 // position c ^ (row & 7) of its 128-byte line: the SWIZZLE_128B pattern TMA and UMMA use.
-__device__ __forceinline__ void put8_kmajor(uint8_t* tile, int r, int c0, const uint32_t w[4]) {
-  uint8_t* line = tile + (c0 >> 6) * 16384 + r * 128;
-  *reinterpret_cast<uint4*>(line + ((((c0 & 63) >> 3) ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+__device__ __forceinline__ void put8_kmajor(uint32_t tile_saddr, int r, int c0, const uint32_t w[4]) {
+  sts128(tile_saddr + (c0 >> 6) * 16384 + r * 128 + ((((c0 & 63) >> 3) ^ (r & 7)) << 4), w);
 }
 
 // ------------------------------------------------------------------------------------------------ forward
@@ -331,6 +341,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   const int qi = qb * QB + r;                                      // position of this thread's query in its sequence
   const uint32_t lane_off = static_cast<uint32_t>((warp & 3) * 32) << 16;
   const float sl2 = p.scale * kLog2e;  // scale > 0 (checked on the host): max(scale * s) = scale * max(s)
+  const uint32_t sP_addr = smem_u32(sP);
   float m_raw = -INFINITY;             // pass 0: running maximum of this thread's half of the row, unscaled
   float m2 = 0.f, l = 0.f;             // pass 1: the row's maximum in the exp2 domain (0 if it sees no key), partial sum
   bool row_empty = false;
@@ -401,7 +412,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         l += l0 + l1;
         if (u > 0) mbar_wait_poll(bar_o, (u - 1) & 1);  // P.V of the previous tile has read the P tile
 #pragma unroll
-        for (int q8 = 0; q8 < 8; ++q8) put8_kmajor(sP, r, half * 64 + q8 * 8, &w[q8 * 4]);
+        for (int q8 = 0; q8 < 8; ++q8) put8_kmajor(sP_addr, r, half * 64 + q8 * 8, &w[q8 * 4]);
         fence_async_shared();  // P was written through the generic proxy; the MMA reads it through the async one
         tc_fence_before();
         mbar_arrive(&bar_done[bi]);
@@ -507,8 +518,8 @@ __device__ __forceinline__ void mma_k64_mn(uint32_t tmem_d, const uint8_t* a, co
     e_umma_bf16(tmem_d, desc_at(aa, k * 32), desc_at(bb, k * 2048), idesc, (accumulate || k != 0) ? 1u : 0u);
 }
 // Row `r` of a [128 x 64] K-major tile: 8 consecutive bf16 values at columns c0 .. c0 + 7 (c0 < 64).
-__device__ __forceinline__ void put8_row64(uint8_t* tile, int r, int c0, const uint32_t w[4]) {
-  *reinterpret_cast<uint4*>(tile + r * 128 + (((c0 >> 3) ^ (r & 7)) << 4)) = make_uint4(w[0], w[1], w[2], w[3]);
+__device__ __forceinline__ void put8_row64(uint32_t tile_saddr, int r, int c0, const uint32_t w[4]) {
+  sts128(tile_saddr + r * 128 + (((c0 >> 3) ^ (r & 7)) << 4), w);
 }
 // Per-64-key flags: the sub-block holds no padding.  Called by the 256 row threads.
 __device__ __forceinline__ void key_sub_flags(const uint8_t* mrow, int T, uint8_t* sub_ok, int tid, int lane) {
@@ -670,12 +681,12 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       const bool all_vis = (is_lo + t) * SB >= kb * QB + QB - 1 &&
                            (p.window <= 0 || (is_lo + t) * SB + SB - 1 - p.window < kb * QB);
       // (log2-sum-exp, scale * delta) of this thread's 32 queries, two queries per 16-byte broadcast read
-      const float4* sq = reinterpret_cast<const float4*>(stat + st * SB + half * 32);
+      const uint32_t sq = smem_u32(stat + st * SB + half * 32);
       uint32_t wp[16], wd[16];
       if (all_vis && key_ok) {
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
-          const float4 sd = sq[e];
+          const float4 sd = lds128f(sq + e * 16);
           const float p0 = fast_exp2(fmaf(v[2 * e], sl2, -sd.x)), p1 = fast_exp2(fmaf(v[2 * e + 1], sl2, -sd.z));
           wp[e] = pack2(p0, p1);
           wd[e] = pack2(p0 * fmaf(g[2 * e], p.scale, -sd.y), p1 * fmaf(g[2 * e + 1], p.scale, -sd.w));
@@ -686,7 +697,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         if (!key_ok) bits = 0u;
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
-          const float4 sd = sq[e];
+          const float4 sd = lds128f(sq + e * 16);
           float p0 = fast_exp2(fmaf(v[2 * e], sl2, -sd.x)), p1 = fast_exp2(fmaf(v[2 * e + 1], sl2, -sd.z));
           if (!((bits >> (2 * e)) & 1u)) p0 = 0.f;
           if (!((bits >> (2 * e + 1)) & 1u)) p1 = 0.f;
@@ -695,8 +706,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         }
       }
       if (t >= 2) mbar_wait_poll(&bar_o[sb], ((t - 2) >> 1) & 1);  // the MMAs that read these two buffers are done
-      uint8_t* pt = sPT + sb * 16384;
-      uint8_t* dst = sDST + sb * 16384;
+      const uint32_t pt = smem_u32(sPT + sb * 16384), dst = smem_u32(sDST + sb * 16384);
 #pragma unroll
       for (int q8 = 0; q8 < 4; ++q8) {
         put8_row64(pt, r, half * 32 + q8 * 8, &wp[q8 * 4]);
@@ -855,7 +865,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         wd[e] = pack2(p0 * fmaf(g[2 * e], p.scale, -dl), p1 * fmaf(g[2 * e + 1], p.scale, -dl));  // dl = scale * delta
       }
       if (t >= 2) mbar_wait_poll(&bar_o[sb], ((t - 2) >> 1) & 1);  // the MMA that read this dS buffer is done
-      uint8_t* ds = sDS + sb * 16384;
+      const uint32_t ds = smem_u32(sDS + sb * 16384);
 #pragma unroll
       for (int q8 = 0; q8 < 4; ++q8) put8_row64(ds, r, half * 32 + q8 * 8, &wd[q8 * 4]);
       fence_async_shared();
