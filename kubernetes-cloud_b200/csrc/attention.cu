@@ -252,8 +252,9 @@ struct FwdSmem {
 // Schedule.  Tiles t = 0 .. 2 nj - 1: pass 0 (row maxima only: no exponentials) over the nj key blocks the query block
 // sees, then pass 1 (P = exp2(s - max) as bf16, row sums in fp32, O += P.V; O / sum at the end).  The scores have two
 // TMEM buffers: while the row threads work on S(t) the tensor pipe already forms S(t+1), and P.V of tile t runs while
-// they work on tile t+1 (they wait for it only at the point where they overwrite the P tile).  K and V each have two
-// shared-memory buffers with their own barriers; a buffer is refilled as soon as the MMA that read it has completed.
+// they work on tile t+1 (they wait for it only at the point where they overwrite the P tile).  In pass 1 K and V each
+// have two shared-memory buffers with their own barriers, refilled as soon as the MMA that read them has completed; in
+// pass 0 all four serve K as one ring.
 template <int DH>
 __global__ void __launch_bounds__(kAttnThreads, 1)
     attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
@@ -309,32 +310,48 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   kv_range(qb, p.window, j_lo, j_hi);
   const int nj = j_hi - j_lo + 1, n_tiles = 2 * nj;
   // (the lambdas below are called by the whole, converged issuing warp: the e_* instructions elect their own lane)
-  auto load_k = [&](int t) {  // K block of tile t -> K buffer t & 1
-    const int bi = t & 1, u = t >= nj ? t - nj : t;
+  // Pass 0 has no use for the V buffers, so K streams through all four tile buffers [K0 K1 V0 V1] as one ring: a K block
+  // is requested four tiles ahead and the TMA latency stays hidden behind the 512 cycles of MMA a tile takes.  The four
+  // barriers bar_k[0..1], bar_v[0..1] are contiguous and serve as the ring's; pass 1 goes on using them per buffer, its
+  // phase counts starting where pass 0 left them (ring_uses).
+  uint64_t* ring_bar = bar_k;
+  auto ring_uses = [&](int s) { return nj > s ? ((nj - 1 - s) >> 2) + 1 : 0; };  // pass-0 tiles that used ring stage s
+  auto load_ring = [&](int t) {  // pass 0: K block of tile t -> ring stage t & 3
+    const int s = t & 3;
+    e_arrive_expect_tx(&ring_bar[s], L::TILE);
+    load_tile<DH>(sK + s * L::TILE, &tmK, &ring_bar[s], b * p.T + (j_lo + t) * QB, col0);
+  };
+  auto issue_s0 = [&](int t) {  // pass 0: S(t) = Q.K(t)^T into S buffer t & 1
+    const int s = t & 3;
+    mbar_wait_poll(&ring_bar[s], (t >> 2) & 1);
+    tc_fence_after();
+    mma_kk<DH>(tmem_s + (t & 1) * 128, sQ, sK + s * L::TILE, 128, false);
+    e_umma_commit(&bar_s[t & 1]);
+  };
+  auto load_k1 = [&](int u) {  // pass 1: K block u -> K buffer u & 1
+    const int bi = u & 1;
     e_arrive_expect_tx(&bar_k[bi], L::TILE);
     load_tile<DH>(sK + bi * L::TILE, &tmK, &bar_k[bi], b * p.T + (j_lo + u) * QB, col0);
   };
-  auto load_v = [&](int u) {  // V block of pass-1 tile u -> V buffer u & 1
+  auto load_v1 = [&](int u) {  // pass 1: V block u -> V buffer u & 1
     const int bi = u & 1;
     e_arrive_expect_tx(&bar_v[bi], L::TILE);
     load_tile<DH>(sV + bi * L::TILE, &tmV, &bar_v[bi], b * p.T + (j_lo + u) * QB, col0);
   };
-  auto issue_s = [&](int t) {  // S(t) = Q.K(t)^T into S buffer t & 1
-    const int bi = t & 1;
-    mbar_wait_poll(&bar_k[bi], (t >> 1) & 1);
+  auto issue_s1 = [&](int u) {  // pass 1: S(nj + u) into S buffer (nj + u) & 1
+    const int bi = u & 1, t = nj + u;
+    mbar_wait_poll(&bar_k[bi], (ring_uses(bi) + (u >> 1)) & 1);
     tc_fence_after();
-    mma_kk<DH>(tmem_s + bi * 128, sQ, sK + bi * L::TILE, 128, false);
-    e_umma_commit(&bar_s[bi]);
+    mma_kk<DH>(tmem_s + (t & 1) * 128, sQ, sK + bi * L::TILE, 128, false);
+    e_umma_commit(&bar_s[t & 1]);
   };
   if (issue_warp) {
     e_arrive_expect_tx(bar_q, L::TILE);
     load_tile<DH>(sQ, &tmQ, bar_q, row0, col0);
-    load_k(0);
-    load_k(1);  // n_tiles >= 2
-    load_v(0);
-    if (nj > 1) load_v(1);
+    for (int t = 0; t < 4 && t < nj; ++t) load_ring(t);
     mbar_wait_poll(bar_q, 0);
-    issue_s(0);
+    issue_s0(0);
+    if (nj > 1) issue_s0(1);
   }
 
   const int r = threadIdx.x & 127, half = (threadIdx.x >> 7) & 1;  // row threads: accumulator row and column half
@@ -349,23 +366,39 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   // No block-wide barrier inside the loop: the row threads report each tile on bar_done and move on, so the eight
   // warps drift apart by up to a tile and one warp's TMEM-load / MUFU latencies hide behind another's arithmetic.
   if (issue_warp) {
-    for (int t = 0; t < n_tiles; ++t) {
-      const int pass = t >= nj, u = pass ? t - nj : t, bi = t & 1;
-      mbar_wait_poll(&bar_s[bi], (t >> 1) & 1);  // S(t) is complete: its K buffer is free
-      if (t + 2 < n_tiles) load_k(t + 2);
-      if (t + 1 < n_tiles) {
-        if (t >= 1) mbar_wait_poll(&bar_done[(t + 1) & 1], ((t - 1) >> 1) & 1);  // tile t-1 has left that S buffer
-        issue_s(t + 1);
+    // pass 0: two S tiles in flight; S(t+2) goes into the TMEM buffer the row threads have just left
+    for (int t = 0; t < nj; ++t) {
+      mbar_wait_poll(&bar_s[t & 1], (t >> 1) & 1);  // S(t) is complete: its ring stage is free
+      if (t + 4 < nj) load_ring(t + 4);
+      if (t + 2 < nj) {
+        mbar_wait_poll(&bar_done[t & 1], (t >> 1) & 1);  // tile t has left its S buffer
+        issue_s0(t + 2);
       }
-      if (pass) {
-        mbar_wait_poll(&bar_done[bi], (t >> 1) & 1);  // P(u) is in shared memory
-        if (u > 0) mbar_wait_poll(bar_o, (u - 1) & 1);  // (complete: the row threads waited for it) V buffer (u+1) & 1 is free
-        if (u >= 1 && u + 1 < nj) load_v(u + 1);
-        mbar_wait_poll(&bar_v[u & 1], (u >> 1) & 1);
-        tc_fence_after();
-        mma_k_mn<DH>(tmem_o, sP, sV + (u & 1) * L::TILE, u != 0);  // first tile of pass 1 overwrites
-        e_umma_commit(bar_o);
+    }
+    // every S of pass 0 is complete: all four buffers are free.  Pass 1: K and V through two buffers each.
+    load_k1(0);
+    load_v1(0);
+    if (nj > 1) {
+      load_k1(1);
+      load_v1(1);
+      mbar_wait_poll(&bar_done[nj & 1], ((nj - 2) >> 1) & 1);  // tile nj-2 has left the S buffer S(nj) goes into
+    }
+    issue_s1(0);
+    for (int u = 0; u < nj; ++u) {
+      const int t = nj + u, bi = t & 1;
+      mbar_wait_poll(&bar_s[bi], (t >> 1) & 1);  // S(t) is complete: K buffer u & 1 is free
+      if (u + 2 < nj) load_k1(u + 2);
+      if (u + 1 < nj) {
+        mbar_wait_poll(&bar_done[(t + 1) & 1], ((t - 1) >> 1) & 1);  // tile t-1 has left that S buffer
+        issue_s1(u + 1);
       }
+      mbar_wait_poll(&bar_done[bi], (t >> 1) & 1);    // P(u) is in shared memory
+      if (u > 0) mbar_wait_poll(bar_o, (u - 1) & 1);  // (complete: the row threads waited for it) V buffer (u+1) & 1 is free
+      if (u >= 1 && u + 1 < nj) load_v1(u + 1);
+      mbar_wait_poll(&bar_v[u & 1], (ring_uses(2 + (u & 1)) + (u >> 1)) & 1);
+      tc_fence_after();
+      mma_k_mn<DH>(tmem_o, sP, sV + (u & 1) * L::TILE, u != 0);  // first tile of pass 1 overwrites
+      e_umma_commit(bar_o);
     }
   } else {
     for (int t = 0; t < n_tiles; ++t) {

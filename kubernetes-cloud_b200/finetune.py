@@ -8,7 +8,7 @@ dataset and ordering FT.py:746-772; micro-batch / accumulation / warm-up / weigh
 FT.py:987-998; per-step samples/s as ``PerformanceCallback`` computes it, FT.py:512-522) and swaps in this package's
 pieces: ``TokenizedDataset`` + ``DeviceBatcher`` for the dataset/collator/H2D path, ``compute_loss`` for lm_head + loss,
 ``GradSync`` for DeepSpeed's gradient reduction, ``FusedAdamW`` + ``WarmupLR`` for its optimizer.  The transformer
-trunk is the HF model (third-party, out of this tier's scope).  Flags of the reference that configure things outside
+trunk is the HF model; for GPT-Neo its blocks run on this package's kernels (``trunk.patch_gpt_neo``).  Flags of the reference that configure things outside
 the hot path (wandb, Tensorizer, prompt sampling, checkpoint discovery) are parsed with the reference's own types,
 defaults and validation and then only logged, so the workflow's flag string (finetune-workflow.yaml:267-300) parses
 verbatim (tests/test_host_logic.py feeds it through ``build_parser``).  ``--fp16=true`` is rejected with exit code 1:
