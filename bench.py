@@ -656,7 +656,8 @@ def run_full_step(dev) -> dict:
                 out["modules_rebound"] = trunk.patch_gpt_neo(model)
             if name.endswith("no_recompute"):  # same arithmetic, activations kept in HBM instead of a second forward
                 model.gradient_checkpointing_disable()
-                torch.cuda.reset_peak_memory_stats(dev)
+            torch.cuda.empty_cache()
+            torch.cuda.reset_peak_memory_stats(dev)
             for _ in range(2):
                 step(ours)
             torch.cuda.synchronize(dev)
