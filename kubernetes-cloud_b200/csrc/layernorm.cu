@@ -9,7 +9,7 @@
 //   forward   one warp per row, the row held in registers (16-byte loads, two shuffle reductions: mean, then the
 //             centred sum of squares); writes y, mean, rstd.  Algorithmic bytes: 4 per element (2 read + 2 written).
 //   backward  one block per group of rows, D / 8 threads, each owning 8 consecutive columns: dx needs two row sums
-//             (block reduction, four rows in flight), dgamma / dbeta need column sums, which every thread keeps in
+//             (block reduction, two rows in flight, one wave of resident blocks), dgamma / dbeta need column sums, which every thread keeps in
 //             registers for its own columns over the block's rows; per-block partial sums go to a workspace and a
 //             second small kernel adds them in a fixed order (deterministic, no atomics).  dx (+)= the gradient that
 //             reached the LayerNorm's input along the residual branch, when given.  Algorithmic bytes: 6 per element
@@ -119,9 +119,10 @@ __global__ void __launch_bounds__(kFwdWarps * 32)
   }
 }
 
-// R rows in flight per block iteration; blockDim.x = D / 8 (a multiple of 32, at most kMaxT).
-template <int R, int kMaxT>
-__global__ void __launch_bounds__(kMaxT)
+// R rows in flight per block iteration; blockDim.x = D / 8 (a multiple of 32, at most kMaxT); kMinBlocks resident
+// blocks per SM are asked of the register allocator (the grid is sized to exactly that many, see plan_bwd).
+template <int R, int kMaxT, int kMinBlocks>
+__global__ void __launch_bounds__(kMaxT, kMinBlocks)
     ln_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
                   const __nv_bfloat16* __restrict__ gamma, const float* __restrict__ mean, const float* __restrict__ rstd,
                   const __nv_bfloat16* __restrict__ dx_add, __nv_bfloat16* __restrict__ dx, float* __restrict__ part,
@@ -138,7 +139,7 @@ __global__ void __launch_bounds__(kMaxT)
   const int64_t r1 = (r0 + rows_per_block < M) ? r0 + rows_per_block : M;
   int it = 0;
   for (int64_t row = r0; row < r1; row += R, ++it) {
-    uint4 xw[R], dw[R];
+    uint4 xw[R], dw[R], aw[R];  // the residual gradient is fetched with the rest: after the reduction its latency would be exposed
     float mu[R], rs[R], s1[R], s2[R];
 #pragma unroll
     for (int rr = 0; rr < R; ++rr) {
@@ -146,6 +147,7 @@ __global__ void __launch_bounds__(kMaxT)
       const size_t off = static_cast<size_t>(row + rr) * D + col;
       xw[rr] = ok ? ld_stream(x + off) : make_uint4(0, 0, 0, 0);
       dw[rr] = ok ? ld_stream(dy + off) : make_uint4(0, 0, 0, 0);
+      aw[rr] = (ok && dx_add != nullptr) ? ld_stream(dx_add + off) : make_uint4(0, 0, 0, 0);
       mu[rr] = ok ? mean[row + rr] : 0.f;
       rs[rr] = ok ? rstd[row + rr] : 0.f;
     }
@@ -196,7 +198,7 @@ __global__ void __launch_bounds__(kMaxT)
       }
       if (dx_add != nullptr) {
         float av[8];
-        unpack8(ld_stream(dx_add + off), av);
+        unpack8(aw[rr], av);
 #pragma unroll
         for (int e = 0; e < 8; ++e) o[e] += av[e];
       }
@@ -239,12 +241,15 @@ __global__ void __launch_bounds__(256) ln_bwd_finalize_kernel(const float* __res
   }
 }
 
-constexpr int kBwdRows = 4;
+constexpr int kBwdRows = 2;  // rows in flight per block iteration (x, dy and the residual gradient of each)
 
-// How the backward cuts the rows: at most 4 blocks per SM, every block a multiple of kBwdRows rows.
-void plan_bwd(int64_t M, int sm_count, int* n_blocks, int* rows_per_block) {
+// Resident blocks per SM the backward is compiled for, by block size (D / 8 threads).
+constexpr int bwd_blocks_per_sm(int threads) { return threads <= 256 ? 3 : 1; }
+
+// How the backward cuts the rows: one wave of resident blocks (no tail wave), every block a multiple of kBwdRows rows.
+void plan_bwd(int64_t M, int D, int sm_count, int* n_blocks, int* rows_per_block) {
   int64_t blocks = (M + kBwdRows - 1) / kBwdRows;
-  const int64_t cap = static_cast<int64_t>(sm_count) * 4;
+  const int64_t cap = static_cast<int64_t>(sm_count) * bwd_blocks_per_sm(D / 8);
   if (blocks > cap) blocks = cap;
   int64_t rpb = (M + blocks - 1) / blocks;
   rpb = (rpb + kBwdRows - 1) / kBwdRows * kBwdRows;
@@ -294,7 +299,7 @@ extern "C" size_t ftk_layernorm_bwd_workspace(int64_t M, int32_t D) {
   ftk::DeviceInfo di;
   if (ftk::get_device_info(&di) != FTK_OK) return 0;
   int n_blocks, rpb;
-  plan_bwd(M, di.sm_count, &n_blocks, &rpb);
+  plan_bwd(M, D, di.sm_count, &n_blocks, &rpb);
   return static_cast<size_t>(n_blocks) * 2 * D * sizeof(float);
 }
 
@@ -309,7 +314,7 @@ extern "C" int ftk_layernorm_bwd(const void* dY, const void* X, const void* gamm
   ftk::DeviceInfo di;
   if (int rc = ftk::get_device_info(&di)) return rc;
   int n_blocks, rpb;
-  plan_bwd(M, di.sm_count, &n_blocks, &rpb);
+  plan_bwd(M, D, di.sm_count, &n_blocks, &rpb);
   const size_t need = static_cast<size_t>(n_blocks) * 2 * D * sizeof(float);
   if (workspace_bytes < need)
     return ftk::fail(FTK_EWORKSPACE, "ftk_layernorm_bwd: workspace %zu bytes < required %zu", workspace_bytes, need);
@@ -318,21 +323,19 @@ extern "C" int ftk_layernorm_bwd(const void* dY, const void* X, const void* gamm
   const int threads = D / 8;
   const size_t smem = static_cast<size_t>(2) * (threads / 32) * 2 * kBwdRows * sizeof(float);
   ftk::TimelineScope tl_(FTK_TL_LAYERNORM_BWD, st);
+  const auto* dy_ = static_cast<const __nv_bfloat16*>(dY);
+  const auto* x_ = static_cast<const __nv_bfloat16*>(X);
+  const auto* g_ = static_cast<const __nv_bfloat16*>(gamma);
+  const auto* add_ = static_cast<const __nv_bfloat16*>(dx_add);
+  auto* dx_ = static_cast<__nv_bfloat16*>(dX);
   if (threads <= 256)
-    ln_bwd_kernel<kBwdRows, 256><<<n_blocks, threads, smem, st>>>(
-        static_cast<const __nv_bfloat16*>(dY), static_cast<const __nv_bfloat16*>(X),
-        static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<const __nv_bfloat16*>(dx_add),
-        static_cast<__nv_bfloat16*>(dX), part, M, D, rpb);
+    ln_bwd_kernel<kBwdRows, 256, bwd_blocks_per_sm(256)><<<n_blocks, threads, smem, st>>>(dy_, x_, g_, mean, rstd, add_, dx_,
+                                                                                          part, M, D, rpb);
   else if (threads <= 512)
-    ln_bwd_kernel<kBwdRows, 512><<<n_blocks, threads, smem, st>>>(
-        static_cast<const __nv_bfloat16*>(dY), static_cast<const __nv_bfloat16*>(X),
-        static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<const __nv_bfloat16*>(dx_add),
-        static_cast<__nv_bfloat16*>(dX), part, M, D, rpb);
+    ln_bwd_kernel<kBwdRows, 512, bwd_blocks_per_sm(512)><<<n_blocks, threads, smem, st>>>(dy_, x_, g_, mean, rstd, add_, dx_,
+                                                                                          part, M, D, rpb);
   else
-    ln_bwd_kernel<2, 1024><<<n_blocks, threads, smem, st>>>(
-        static_cast<const __nv_bfloat16*>(dY), static_cast<const __nv_bfloat16*>(X),
-        static_cast<const __nv_bfloat16*>(gamma), mean, rstd, static_cast<const __nv_bfloat16*>(dx_add),
-        static_cast<__nv_bfloat16*>(dX), part, M, D, rpb);
+    ln_bwd_kernel<kBwdRows, 1024, 1><<<n_blocks, threads, smem, st>>>(dy_, x_, g_, mean, rstd, add_, dx_, part, M, D, rpb);
   FTK_CUDA_CHECK(cudaGetLastError());
   ln_bwd_finalize_kernel<<<(D + 31) / 32, 256, 0, st>>>(part, n_blocks, D, dgamma, dbeta);
   FTK_CUDA_CHECK(cudaGetLastError());

@@ -947,21 +947,42 @@ __global__ void __launch_bounds__(256) dh_reduce_kernel(const float* __restrict_
   }
 }
 
-// dbias[v] += sum over slab rows of dZ[row, v].
-__global__ void __launch_bounds__(128) dbias_kernel(const __nv_bfloat16* __restrict__ dz, int rows, int V, int ld,
+// dbias[v] += sum over slab rows of dZ[row, v].  HBM bound: a block covers 256 columns x rows_per_block rows, a lane
+// 8 consecutive columns (16-byte loads, a warp reads 512 contiguous bytes of a row, four rows in flight per warp), its
+// eight warps take every eighth row; one shared-memory reduction and one atomicAdd per column and block.
+__global__ void __launch_bounds__(256) dbias_kernel(const __nv_bfloat16* __restrict__ dz, int rows, int V, int ld,
                                                     int rows_per_block, float* __restrict__ dbias) {
-  const int col = (blockIdx.x * 128 + threadIdx.x) * 2;
-  if (col >= V) return;
+  __shared__ float part[8][257];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int col = blockIdx.x * 256 + lane * 8;
   const int r0 = blockIdx.y * rows_per_block;
   const int r1 = min(rows, r0 + rows_per_block);
-  float a0 = 0.f, a1 = 0.f;
-  for (int r = r0; r < r1; ++r) {
-    const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(dz + static_cast<size_t>(r) * ld + col);
-    a0 += __low2float(h);
-    a1 += __high2float(h);
+  float acc[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+  if (col < ld) {
+#pragma unroll 4
+    for (int r = r0 + warp; r < r1; r += 8) {
+      const uint4 w = __ldg(reinterpret_cast<const uint4*>(dz + static_cast<size_t>(r) * ld + col));
+      const uint32_t u[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&u[e]);
+        acc[2 * e] += __low2float(h);
+        acc[2 * e + 1] += __high2float(h);
+      }
+    }
   }
-  atomicAdd(dbias + col, a0);
-  if (col + 1 < V) atomicAdd(dbias + col + 1, a1);
+#pragma unroll
+  for (int e = 0; e < 8; ++e) part[warp][lane * 8 + e] = acc[e];
+  __syncthreads();
+  const int c = blockIdx.x * 256 + threadIdx.x;
+  if (c < V) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += part[w][threadIdx.x];
+    atomicAdd(dbias + c, t);
+  }
 }
 
 
@@ -1454,7 +1475,7 @@ int run_grad_gemms(const void* H, const void* W, int64_t rows, int d, int V, voi
     ftk::TimelineScope tl_(FTK_TL_DBIAS, st);
     const int rows_per_block = 256;
     dim3 grid(ceil_div(V, 256), ceil_div(rows, rows_per_block));
-    dbias_kernel<<<grid, 128, 0, st>>>(dz, static_cast<int>(rows), V, static_cast<int>(dz_pitch(V)), rows_per_block,
+    dbias_kernel<<<grid, 256, 0, st>>>(dz, static_cast<int>(rows), V, static_cast<int>(dz_pitch(V)), rows_per_block,
                                        dbias);
     FTK_CUDA_CHECK(cudaGetLastError());
   }
@@ -2030,7 +2051,7 @@ extern "C" int ftk_linear_bwd(const void* X, const void* W, const void* dY, cons
     ftk::TimelineScope tl_(FTK_TL_DBIAS, st);
     const int rows_per_block = 256;
     dim3 grid(ceil_div(N, 256), ceil_div(M, rows_per_block));
-    dbias_kernel<<<grid, 128, 0, st>>>(static_cast<const __nv_bfloat16*>(dY), static_cast<int>(M), N, N, rows_per_block,
+    dbias_kernel<<<grid, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(dY), static_cast<int>(M), N, N, rows_per_block,
                                        dbias);
     FTK_CUDA_CHECK(cudaGetLastError());
   }
