@@ -40,8 +40,10 @@ constexpr int QB = 128;            // rows of a block (queries or keys) = TMEM l
 // Warps 0-7: row threads.  Thread t owns accumulator row t % 128 (warp w reads TMEM lanes 32 * (w % 4)) and the column
 // half t / 128 of every tile, so each row is worked on by two threads on the same SM sub-partition: with a single warp
 // per scheduler nothing hid the TMEM-load and MUFU latencies (ncu: issue slots 22 % busy, tensor pipe 15 %).
-// Warp 8: TMA + MMA issue (lane 0), TMEM allocation.
-constexpr int kAttnThreads = 288;
+// Warp 8: TMA loads + the score MMAs (S, dP), TMEM allocation.  Warp 9: the MMAs that consume what the row threads wrote
+// (P.V, the gradient accumulations).  Two issuing warps because a tcgen05.mma issue is paced by the tensor pipe: one
+// warp doing both spent a tile's MMA time twice in series, with its barrier waits and TMA issue on top.
+constexpr int kAttnThreads = 320;
 constexpr int kRowThreads = 256;
 constexpr int kIssuerWarp = 8;
 constexpr float kLog2e = 1.4426950408889634f;
@@ -298,7 +300,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   if (warp == kIssuerWarp) {
     tmem_alloc<1>(tmem_slot, 512);
     tmem_relinquish<1>();
-  } else if (mrow != nullptr) {
+  } else if (mrow != nullptr && warp < kIssuerWarp) {
     key_block_flags(mrow, p.T, blk_ok, threadIdx.x, lane);
   }
   tc_fence_before();
@@ -375,25 +377,35 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
         issue_s0(t + 2);
       }
     }
-    // every S of pass 0 is complete: all four buffers are free.  Pass 1: K and V through two buffers each.
+    // every S of pass 0 is complete: the K buffers are free (the other warp refills the V buffers).  Pass 1: K through
+    // two buffers, S one tile ahead of the row threads.
     load_k1(0);
-    load_v1(0);
     if (nj > 1) {
       load_k1(1);
-      load_v1(1);
       mbar_wait_poll(&bar_done[nj & 1], ((nj - 2) >> 1) & 1);  // tile nj-2 has left the S buffer S(nj) goes into
     }
     issue_s1(0);
-    for (int u = 0; u < nj; ++u) {
-      const int t = nj + u, bi = t & 1;
-      mbar_wait_poll(&bar_s[bi], (t >> 1) & 1);  // S(t) is complete: K buffer u & 1 is free
+    for (int u = 0; u + 1 < nj; ++u) {
+      const int t = nj + u;
+      mbar_wait_poll(&bar_s[t & 1], (t >> 1) & 1);  // S(t) is complete: K buffer u & 1 is free
       if (u + 2 < nj) load_k1(u + 2);
-      if (u + 1 < nj) {
-        mbar_wait_poll(&bar_done[(t + 1) & 1], ((t - 1) >> 1) & 1);  // tile t-1 has left that S buffer
-        issue_s1(u + 1);
-      }
-      mbar_wait_poll(&bar_done[bi], (t >> 1) & 1);    // P(u) is in shared memory
-      if (u > 0) mbar_wait_poll(bar_o, (u - 1) & 1);  // (complete: the row threads waited for it) V buffer (u+1) & 1 is free
+      mbar_wait_poll(&bar_done[(t + 1) & 1], ((t - 1) >> 1) & 1);  // tile t-1 has left that S buffer
+      issue_s1(u + 1);
+    }
+  } else if (warp == kIssuerWarp + 1) {  // V ring + the P.V MMAs of pass 1
+    // Pass 0: only follow the barriers.  A parity wait is valid only for the phase right after the last one this warp
+    // saw complete (a wait for phase k on a barrier still in phase k-2 returns at once), so every phase is awaited.
+    for (int t = 0; t < nj; ++t) {
+      mbar_wait_poll(&bar_s[t & 1], (t >> 1) & 1);
+      mbar_wait_poll(&bar_done[t & 1], (t >> 1) & 1);
+    }
+    // every S of pass 0 is complete and read: the V buffers (ring stages 2, 3) are free
+    load_v1(0);
+    if (nj > 1) load_v1(1);
+    for (int u = 0; u < nj; ++u) {
+      const int t = nj + u;
+      mbar_wait_poll(&bar_done[t & 1], (t >> 1) & 1);  // P(u) is in shared memory
+      if (u > 0) mbar_wait_poll(bar_o, (u - 1) & 1);   // P.V(u-1) done: V buffer (u + 1) & 1 is free
       if (u >= 1 && u + 1 < nj) load_v1(u + 1);
       mbar_wait_poll(&bar_v[u & 1], (ring_uses(2 + (u & 1)) + (u >> 1)) & 1);
       tc_fence_after();
@@ -685,14 +697,19 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   if (warp < kIssuerWarp && p.key_mask != nullptr) key_ok = p.key_mask[static_cast<size_t>(b) * p.T + kj] != 0;
 
   // No block-wide barrier inside the loop (see the forward kernel): the row threads report on bar_done and move on.
-  if (issue_warp) {
+  if (issue_warp) {  // operand ring + score MMAs, one sub-tile ahead of the row threads
+    for (int t = 0; t + 1 < n; ++t) {
+      if (t >= 1) {
+        mbar_wait_poll(&bar_o[(t - 1) & 1], ((t - 1) >> 1) & 1);     // gradient MMAs of t-1 done: ring stage (t + 2) % 3 is free
+        mbar_wait_poll(&bar_done[(t + 1) & 1], ((t - 1) >> 1) & 1);  // row threads have left TMEM buffer (t + 1) & 1
+      }
+      if (t + 2 < n) load_qd(t + 2);
+      issue_s(t + 1);
+    }
+  } else if (warp == kIssuerWarp + 1) {  // gradient MMAs
     for (int t = 0; t < n; ++t) {
       const int sb = t & 1, st = t % 3;
-      mbar_wait_poll(&bar_s[sb], (t >> 1) & 1);
-      if (t >= 1) mbar_wait_poll(&bar_o[(t - 1) & 1], ((t - 1) >> 1) & 1);  // ring stage (t + 2) % 3 is free again
-      if (t + 2 < n) load_qd(t + 2);
-      // TMEM buffer (t + 1) & 1 was last read for sub-tile t - 1, whose bar_done was awaited an iteration ago
-      if (t + 1 < n) issue_s(t + 1);
+      mbar_wait_poll(&bar_qd[st], (t / 3) & 1);     // (complete) this warp's own acquire of the stage's TMA writes
       mbar_wait_poll(&bar_done[sb], (t >> 1) & 1);  // P^T(t) and dS^T(t) are in shared memory
       tc_fence_after();
       mma_k64_mn<DH>(tmem_dv, sPT + sb * 16384, sDO + st * L::SUB, t != 0);  // dV += P^T . dO_i
@@ -819,7 +836,7 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
   if (warp == kIssuerWarp) {
     tmem_alloc<1>(tmem_slot, 512);
     tmem_relinquish<1>();
-  } else if (mrow != nullptr) {
+  } else if (mrow != nullptr && warp < kIssuerWarp) {
     key_sub_flags(mrow, p.T, sub_ok, threadIdx.x, lane);
   }
   tc_fence_before();
@@ -865,13 +882,19 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
     dl = sd.y;
   }
 
-  if (issue_warp) {
+  if (issue_warp) {  // operand ring + score MMAs, one sub-tile ahead of the row threads
+    for (int t = 0; t + 1 < n; ++t) {
+      if (t >= 1) {
+        mbar_wait_poll(&bar_o[(t - 1) & 1], ((t - 1) >> 1) & 1);     // dQ MMA of t-1 done: ring stage (t + 2) % 3 is free
+        mbar_wait_poll(&bar_done[(t + 1) & 1], ((t - 1) >> 1) & 1);  // row threads have left TMEM buffer (t + 1) & 1
+      }
+      if (t + 2 < n) load_kv(t + 2);
+      issue_s(t + 1);
+    }
+  } else if (warp == kIssuerWarp + 1) {  // dQ MMAs
     for (int t = 0; t < n; ++t) {
       const int sb = t & 1, st = t % 3;
-      mbar_wait_poll(&bar_s[sb], (t >> 1) & 1);
-      if (t >= 1) mbar_wait_poll(&bar_o[(t - 1) & 1], ((t - 1) >> 1) & 1);  // ring stage (t + 2) % 3 is free again
-      if (t + 2 < n) load_kv(t + 2);
-      if (t + 1 < n) issue_s(t + 1);  // its TMEM buffer was last read for sub-tile t - 1 (bar_done awaited then)
+      mbar_wait_poll(&bar_kv[st], (t / 3) & 1);     // (complete) this warp's own acquire of the stage's TMA writes
       mbar_wait_poll(&bar_done[sb], (t >> 1) & 1);  // dS(t) is in shared memory
       tc_fence_after();
       mma_k64_mn<DH>(tmem_dq, sDS + sb * 16384, sK + st * L::SUB, t != 0);  // dQ += dS . K_j
