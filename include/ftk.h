@@ -281,7 +281,8 @@ int ftk_scale_unless_one(void* buf, size_t n, int32_t dtype, const float* factor
  *                    instead of leaving two elementwise sums to autograd;
  *                    dW[N,K] (+)= dY^T . X           (NULL to skip; FTK_BF16 / FTK_F32, accumulate as elsewhere);
  *                    dbias[N] (+)= column sums of dY  (fp32, NULL to skip)
- * K and N must be multiples of 64.
+ * K and N must be multiples of 64; Y, pre, residual, dX, dW, dx_mul_pre and dx_add 32-byte aligned (the epilogues use
+ * 32-byte accesses: a thread owns a row, and 16-byte accesses would leave every sector half written per instruction).
  */
 #define FTK_ACT_NONE 0
 #define FTK_ACT_GELU_NEW 1

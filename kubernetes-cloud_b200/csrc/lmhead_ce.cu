@@ -92,7 +92,17 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 struct EpiCtx {
   uint8_t* smem;
   int q, lane;
+  int half;  // epilogues with kColSplit: which half of every tile's columns this warp handles (else 0)
 };
+
+// Threads per CTA: warp 0 TMA, 1 MMA, 2 TMEM allocation, 3 idle, 4-7 epilogue (one accumulator row per thread), and
+// for epilogues that declare kColSplit four more epilogue warps (8-11) on the other half of every tile's columns.
+template <class Epi, class = void>
+struct EpiColSplit { static constexpr bool value = false; };
+template <class Epi>
+struct EpiColSplit<Epi, decltype(void(Epi::kColSplit))> { static constexpr bool value = Epi::kColSplit; };
+template <class Epi>
+constexpr int threads_of() { return EpiColSplit<Epi>::value ? 384 : 256; }
 
 // Forward: online softmax statistics over this unit's vocabulary chunk.
 struct FwdEpi {
@@ -397,6 +407,23 @@ struct FwdKeepEpi {
   }
 };
 
+// 32-byte global accesses (STG.E.ENL2.256 / LDG.E.ENL2.256).  An epilogue thread owns one accumulator row, so a warp's
+// store instruction touches 32 different rows: with 16-byte accesses every one of them is half a 32-byte sector and the
+// L2 has to merge two partial writes per sector (the c_fc GEMM that also stores its pre-activation ran at 868 TF/s
+// with 16-byte stores and at 1326 TF/s, the speed of the plain GEMM, with 32-byte ones).
+__device__ __forceinline__ void st_global_32B(void* p, const uint32_t w[8]) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]),
+               "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+               : "memory");
+}
+
+__device__ __forceinline__ void ld_global_32B(const void* p, uint32_t w[8]) {
+  asm volatile("ld.global.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
+               : "l"(p)
+               : "memory");
+}
+
 // Plain GEMM epilogue: out[row, col] (+)= acc, bf16 or fp32 row-major.  Under split-K each split writes its partial
 // sums to its own copy of the output, split_stride elements apart (summed afterwards in a fixed order).
 template <bool kF32>
@@ -428,8 +455,49 @@ struct StoreEpi {
       float v[32];
       tmem_ld32(taddr + c * 32, v);
       tmem_ld_wait();
+      // 32-byte accesses when the chunk is whole and the output is 32-byte aligned (always, for the callers in this
+      // library: d is a multiple of 64 and the buffers come from an allocator); otherwise the 16-byte path below
+      const bool wide = col0 + 32 <= p.cols && (p.ld & 15) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 31) == 0 &&
+                        (st.base & 15) == 0;
       if (st.row >= p.rows) {
         // rows past the end: nothing to store (no `continue`: the next tcgen05.ld needs a converged warp)
+      } else if (wide) {
+        if constexpr (kF32) {
+          float* dst = static_cast<float*>(p.out) + st.base + static_cast<size_t>(st.row) * p.ld + col0;
+          if (p.accumulate) {
+#pragma unroll
+            for (int g8 = 0; g8 < 4; ++g8) {
+              uint32_t old[8];
+              ld_global_32B(dst + g8 * 8, old);
+#pragma unroll
+              for (int e = 0; e < 8; ++e) v[g8 * 8 + e] += __uint_as_float(old[e]);
+            }
+          }
+#pragma unroll
+          for (int g8 = 0; g8 < 4; ++g8) st_global_32B(dst + g8 * 8, reinterpret_cast<const uint32_t*>(v + g8 * 8));
+        } else {
+          __nv_bfloat16* dst = static_cast<__nv_bfloat16*>(p.out) + st.base + static_cast<size_t>(st.row) * p.ld + col0;
+          if (p.accumulate) {
+#pragma unroll
+            for (int g16 = 0; g16 < 2; ++g16) {
+              uint32_t old[8];
+              ld_global_32B(dst + g16 * 16, old);
+#pragma unroll
+              for (int e = 0; e < 8; ++e) {
+                const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&old[e]);
+                v[g16 * 16 + 2 * e] += __low2float(h);
+                v[g16 * 16 + 2 * e + 1] += __high2float(h);
+              }
+            }
+          }
+#pragma unroll
+          for (int g16 = 0; g16 < 2; ++g16) {
+            uint32_t w[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) w[e] = pack_bf16x2(v[g16 * 16 + 2 * e], v[g16 * 16 + 2 * e + 1]);
+            st_global_32B(dst + g16 * 16, w);
+          }
+        }
       } else if constexpr (kF32) {
         float4* dst = reinterpret_cast<float4*>(static_cast<float*>(p.out) + st.base + static_cast<size_t>(st.row) * p.ld + col0);
 #pragma unroll
@@ -482,6 +550,10 @@ struct StoreEpi {
 //             connection in the forward, the sum of several layers' input gradients in the backward.  May alias out.
 struct LinearEpi {
   static constexpr uint32_t kSmemBytes = 0;
+  // Two threads per accumulator row, each on half of the tile's columns: with K = 2048 a 256 x 256 tile's MMAs take
+  // ~12 us and the gelu_new + two-store epilogue of c_fc took longer than that on four warps (868 TF/s against 1271
+  // for the plain GEMM).
+  static constexpr bool kColSplit = true;
   struct Params {
     __nv_bfloat16* out;
     __nv_bfloat16* pre;
@@ -517,36 +589,41 @@ struct LinearEpi {
   // fetched one chunk ahead: a thread reads its own row, so these loads are latency-, not bandwidth-bound, and left in
   // the chunk's dependency chain they stretch the epilogue past the MMAs of the next tile.
   struct Side {
-    uint4 m[4], r[4];
+    uint32_t m[16], r[16];
   };
   static __device__ __forceinline__ void fetch(Side& sd, const State& st, const Params& p, int col0) {
     if (st.row >= p.rows || col0 >= p.cols) return;
-    const size_t off = static_cast<size_t>(st.row) * p.ld + col0;
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      if (col0 + q * 8 >= p.cols) break;
-      if (p.mul_pre != nullptr) sd.m[q] = *(reinterpret_cast<const uint4*>(p.mul_pre + off) + q);
-      if (p.residual != nullptr) sd.r[q] = *(reinterpret_cast<const uint4*>(p.residual + off) + q);
+    const size_t off = static_cast<size_t>(st.row) * p.ld + col0;  // 64-byte aligned: two 32-byte loads per input
+    if (p.mul_pre != nullptr) {
+      ld_global_32B(p.mul_pre + off, sd.m);
+      ld_global_32B(p.mul_pre + off + 16, sd.m + 8);
+    }
+    if (p.residual != nullptr) {
+      ld_global_32B(p.residual + off, sd.r);
+      ld_global_32B(p.residual + off + 16, sd.r + 8);
     }
   }
   template <int BN>
-  static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0, const EpiCtx&) {
+  static __device__ __forceinline__ void tile(State& st, const Params& p, uint32_t taddr, int n0, const EpiCtx& cx) {
+    constexpr int kChunks = BN / 32 / 2;  // this warp's half of the tile
+    const int c_begin = cx.half * kChunks, c_end = c_begin + kChunks;
     Side nxt = {};
-    fetch(nxt, st, p, n0);
+    fetch(nxt, st, p, n0 + c_begin * 32);
 #pragma unroll 1
-    for (int c = 0; c < BN / 32; ++c) {
+    for (int c = c_begin; c < c_end; ++c) {
       const int col0 = n0 + c * 32;
       if (col0 >= p.cols) break;  // warp-uniform
       float v[32];
       tmem_ld32(taddr + c * 32, v);
       const Side cur = nxt;
-      if (c + 1 < BN / 32) fetch(nxt, st, p, col0 + 32);
+      if (c + 1 < c_end) fetch(nxt, st, p, col0 + 32);
       tmem_ld_wait();
       if (st.row < p.rows) {  // no `continue`: the next tcgen05.ld needs a converged warp
+        // cols is a multiple of 64 (checked on the host), so a 32-column chunk is wholly inside or was skipped above
         const size_t off = static_cast<size_t>(st.row) * p.ld + col0;
+        uint32_t wo[16], wp[16];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          if (col0 + q * 8 >= p.cols) break;  // cols is a multiple of 8
           float* x = v + 8 * q;
           if (p.bias != nullptr) {
             const uint4 bw = __ldg(reinterpret_cast<const uint4*>(p.bias + col0) + q);
@@ -559,7 +636,7 @@ struct LinearEpi {
             }
           }
           if (p.mul_pre != nullptr) {
-            const uint32_t p4[4] = {cur.m[q].x, cur.m[q].y, cur.m[q].z, cur.m[q].w};
+            const uint32_t* p4 = cur.m + 4 * q;
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&p4[e]);
@@ -568,14 +645,13 @@ struct LinearEpi {
             }
           }
           if (p.act == 1) {
-            if (p.pre != nullptr)
-              *(reinterpret_cast<uint4*>(p.pre + off) + q) = make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]),
-                                                                        pack_bf16x2(x[4], x[5]), pack_bf16x2(x[6], x[7]));
+#pragma unroll
+            for (int e = 0; e < 4; ++e) wp[4 * q + e] = pack_bf16x2(x[2 * e], x[2 * e + 1]);
 #pragma unroll
             for (int e = 0; e < 8; ++e) x[e] = gelu_new(x[e]);
           }
           if (p.residual != nullptr) {
-            const uint32_t r4[4] = {cur.r[q].x, cur.r[q].y, cur.r[q].z, cur.r[q].w};
+            const uint32_t* r4 = cur.r + 4 * q;
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&r4[e]);
@@ -583,9 +659,16 @@ struct LinearEpi {
               x[2 * e + 1] += __high2float(h);
             }
           }
-          *(reinterpret_cast<uint4*>(p.out + off) + q) = make_uint4(pack_bf16x2(x[0], x[1]), pack_bf16x2(x[2], x[3]),
-                                                                    pack_bf16x2(x[4], x[5]), pack_bf16x2(x[6], x[7]));
+#pragma unroll
+          for (int e = 0; e < 4; ++e) wo[4 * q + e] = pack_bf16x2(x[2 * e], x[2 * e + 1]);
         }
+        // 32-byte stores: every instruction writes whole 32-byte sectors of this thread's row
+        if (p.act == 1 && p.pre != nullptr) {
+          st_global_32B(p.pre + off, wp);
+          st_global_32B(p.pre + off + 16, wp + 8);
+        }
+        st_global_32B(p.out + off, wo);
+        st_global_32B(p.out + off + 16, wo + 8);
       }
     }
   }
@@ -608,7 +691,7 @@ struct SmemLayout {
 };
 
 template <int kCG, int BN, int kStages, bool kAMN, bool kBMN, class Epi>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(threads_of<Epi>(), 1)
     umma_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const Sched sc,
                 const __grid_constant__ typename Epi::Params ep) {
   using L = SmemLayout<kCG, BN, kStages, Epi::kSmemBytes>;
@@ -643,7 +726,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
     for (int i = 0; i < kAccStages; ++i) {
       mbar_init(&tfull[i], 1);         // tcgen05.commit
-      mbar_init(&tempty[i], kCG * 4);  // one arrive per epilogue warp of each CTA
+      mbar_init(&tempty[i], kCG * (threads_of<Epi>() / 32 - 4));  // one arrive per epilogue warp of each CTA
     }
     fence_mbar_init();
   }
@@ -772,7 +855,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     // ============================== epilogue ==============================
     const int q = warp & 3;  // TMEM lane quarter this warp may access
     const int row_in_tile = q * 32 + lane;
-    const EpiCtx cx{smem + L::EPI_OFF, q, lane};
+    const EpiCtx cx{smem + L::EPI_OFF, q, lane, (warp - 4) >> 2};
     typename Epi::State st = {};
     uint32_t it = 0;
     for (int u = cl; u < sc.n_units; u += n_cl) {
@@ -1065,7 +1148,7 @@ int launch_umma(const CUtensorMap& tmA, const CUtensorMap& tmB, const Sched& sc,
   if (n_cl <= 0) return FTK_OK;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(static_cast<unsigned>(n_cl * kCG));
-  cfg.blockDim = dim3(kThreads);
+  cfg.blockDim = dim3(threads_of<Epi>());
   cfg.dynamicSmemBytes = L::BYTES;
   cfg.stream = st;
   cudaLaunchAttribute attr[1];
@@ -1993,9 +2076,9 @@ extern "C" int ftk_linear_fwd(const void* X, const void* W, const void* bias, co
   if (int rc = check_linear(X, W, M, K, N, &di)) return rc;
   FTK_REQUIRE(Y != nullptr, "ftk_linear_fwd: null output");
   FTK_REQUIRE(act == FTK_ACT_NONE || act == FTK_ACT_GELU_NEW, "ftk_linear_fwd: bad activation code %d", act);
-  FTK_REQUIRE(((reinterpret_cast<uintptr_t>(Y) | reinterpret_cast<uintptr_t>(pre) | reinterpret_cast<uintptr_t>(bias) |
-                reinterpret_cast<uintptr_t>(residual)) & 15) == 0,
-              "ftk_linear_fwd: Y / pre / bias / residual must be 16-byte aligned");
+  FTK_REQUIRE((reinterpret_cast<uintptr_t>(bias) & 15) == 0, "ftk_linear_fwd: bias must be 16-byte aligned");
+  FTK_REQUIRE(((reinterpret_cast<uintptr_t>(Y) | reinterpret_cast<uintptr_t>(pre) | reinterpret_cast<uintptr_t>(residual)) & 31) == 0,
+              "ftk_linear_fwd: Y / pre / residual must be 32-byte aligned");
   LinearEpi::Params ep;
   ep.out = static_cast<__nv_bfloat16*>(Y);
   ep.pre = static_cast<__nv_bfloat16*>(pre);
@@ -2020,8 +2103,8 @@ extern "C" int ftk_linear_bwd(const void* X, const void* W, const void* dY, cons
   FTK_REQUIRE(dY != nullptr, "ftk_linear_bwd: null dY");
   FTK_REQUIRE(dw_dtype == FTK_BF16 || dw_dtype == FTK_F32, "ftk_linear_bwd: bad dw_dtype %d", dw_dtype);
   FTK_REQUIRE(((reinterpret_cast<uintptr_t>(dX) | reinterpret_cast<uintptr_t>(dW) | reinterpret_cast<uintptr_t>(dx_mul_pre) |
-                reinterpret_cast<uintptr_t>(dx_add)) & 15) == 0,
-              "ftk_linear_bwd: dX / dW / dx_mul_pre / dx_add must be 16-byte aligned");
+                reinterpret_cast<uintptr_t>(dx_add)) & 31) == 0,
+              "ftk_linear_bwd: dX / dW / dx_mul_pre / dx_add must be 32-byte aligned");
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const bool pair = cta_group() == 2 && di.sm_count >= 2;
   if (dX != nullptr) {  // dX[M, K] = dY[M, N] . W[N, K]  (times gelu_new'(dx_mul_pre) when given)
