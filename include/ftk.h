@@ -270,25 +270,26 @@ int ftk_scale_unless_one(void* buf, size_t n, int32_t dtype, const float* factor
  * GPT-Neo / GPT-J blocks (the modules finetuner.py trains through model(**inputs), FT.py:479, with gradient
  * checkpointing on, FT.py:884) and the elementwise passes around their MLP activation.
  *   ftk_linear_fwd   Y[M,N] = act(X[M,K] . W[N,K]^T + bias[N]) + residual[M,N], all bf16; bias and residual may be
- *                    NULL; act FTK_ACT_GELU_NEW also stores the pre-activation in `pre` (may be NULL) for the
- *                    backward. The residual (HF GPTNeoBlock.forward's `attn_output + residual` and
+ *                    NULL; act FTK_ACT_GELU_NEW also stores gelu_new'(X . W^T + bias) in `dact` (may be NULL): the
+ *                    factor the backward needs, computed from the same tanh as the activation itself.
+ *                    The residual (HF GPTNeoBlock.forward's `attn_output + residual` and
  *                    `residual + feed_forward_hidden_states`) is added in fp32 before the one rounding to bf16 and
  *                    may alias Y.
- *   ftk_linear_bwd   dX[M,K] = dY[M,N] . W            (NULL to skip), multiplied elementwise by gelu_new'(dx_mul_pre)
- *                    when dx_mul_pre (bf16 [M,K], the pre-activation of the GELU layer that produced X) is given:
- *                    the gradient leaves the GEMM already taken through the activation; plus dx_add[M,K] when given
- *                    (may alias dX): layers that share an input (q_proj, k_proj, v_proj) chain their dX GEMMs
- *                    instead of leaving two elementwise sums to autograd;
+ *   ftk_linear_bwd   dX[M,K] = dY[M,N] . W            (NULL to skip), multiplied elementwise by dx_mul (bf16 [M,K],
+ *                    the `dact` of the GELU layer that produced X) when given: the gradient leaves the GEMM already
+ *                    taken through the activation; plus dx_add[M,K] when given (may alias dX): layers that share an
+ *                    input (q_proj, k_proj, v_proj) chain their dX GEMMs instead of leaving two elementwise sums to
+ *                    autograd;
  *                    dW[N,K] (+)= dY^T . X           (NULL to skip; FTK_BF16 / FTK_F32, accumulate as elsewhere);
  *                    dbias[N] (+)= column sums of dY  (fp32, NULL to skip)
- * K and N must be multiples of 64; Y, pre, residual, dX, dW, dx_mul_pre and dx_add 32-byte aligned (the epilogues use
+ * K and N must be multiples of 64; Y, dact, residual, dX, dW, dx_mul and dx_add 32-byte aligned (the epilogues use
  * 32-byte accesses: a thread owns a row, and 16-byte accesses would leave every sector half written per instruction).
  */
 #define FTK_ACT_NONE 0
 #define FTK_ACT_GELU_NEW 1
 int ftk_linear_fwd(const void* X, const void* W, const void* bias, const void* residual, int64_t M, int32_t K, int32_t N,
-                   int32_t act, void* Y, void* pre, void* stream);
-int ftk_linear_bwd(const void* X, const void* W, const void* dY, const void* dx_mul_pre, const void* dx_add, int64_t M,
+                   int32_t act, void* Y, void* dact, void* stream);
+int ftk_linear_bwd(const void* X, const void* W, const void* dY, const void* dx_mul, const void* dx_add, int64_t M,
                    int32_t K, int32_t N, void* dX, void* dW, int32_t dw_dtype, int32_t accumulate, float* dbias,
                    void* stream);
 

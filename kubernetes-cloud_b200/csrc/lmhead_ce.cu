@@ -542,10 +542,11 @@ struct StoreEpi {
 };
 
 // Linear-layer epilogue (the trunk's projections): bf16 out[row, col] = f(acc + bias[col]).
-//   act == 1: f = gelu_new (the tanh form HF's GPT-Neo / GPT-J MLPs use); `pre` (optional) also receives acc + bias,
-//             the value the backward needs;
-//   mul_pre != null: out = acc * gelu_new'(mul_pre[row, col]) -- the dX GEMM of the layer AFTER a GELU hands back the
-//             gradient with respect to the pre-activation directly, so no elementwise pass ever touches [M, 4d].
+//   act == 1: f = gelu_new (the tanh form HF's GPT-Neo / GPT-J MLPs use); `pre` (optional) receives
+//             gelu_new'(acc + bias), the factor the backward needs (same tanh, a few more FMAs here, none there);
+//   mul_pre != null: out = acc * mul_pre[row, col] -- the dX GEMM of the layer AFTER a GELU multiplies by that saved
+//             derivative and hands back the gradient with respect to the pre-activation directly, so no elementwise
+//             pass ever touches [M, 4d].
 //   residual != null: out += residual[row, col] (last, in fp32 before the one rounding): the block's residual
 //             connection in the forward, the sum of several layers' input gradients in the backward.  May alias out.
 struct LinearEpi {
@@ -570,15 +571,14 @@ struct LinearEpi {
     asm("tanh.approx.f32 %0, %1;" : "=f"(r) : "f"(x));
     return r;
   }
-  static __device__ __forceinline__ float gelu_new(float x) {
-    const float u = 0.7978845608028654f * fmaf(0.044715f * x, x * x, x);
-    return 0.5f * x * (1.f + tanh_fast(u));
-  }
-  static __device__ __forceinline__ float gelu_new_grad(float x) {
+  // y = gelu_new(x) = 0.5 x (1 + tanh(u)), u = sqrt(2/pi) (x + 0.044715 x^3), and dy/dx = 0.5 (1 + t) + 0.5 x (1 - t^2) u'
+  static __device__ __forceinline__ void gelu_new_both(float x, float& y, float& dy) {
     const float x2 = x * x;
     const float t = tanh_fast(0.7978845608028654f * fmaf(0.044715f * x, x2, x));
     const float du = 0.7978845608028654f * fmaf(3.f * 0.044715f, x2, 1.f);
-    return 0.5f * (1.f + t) + 0.5f * x * (1.f - t * t) * du;
+    const float h = 0.5f * (1.f + t);
+    y = x * h;
+    dy = fmaf(0.5f * x * du, fmaf(-t, t, 1.f), h);
   }
   template <int BN>
   static __device__ __forceinline__ void begin_unit(State& st, const Params&, int row, int) {
@@ -635,20 +635,21 @@ struct LinearEpi {
               x[2 * e + 1] += __high2float(h);
             }
           }
-          if (p.mul_pre != nullptr) {
+          if (p.mul_pre != nullptr) {  // the saved gelu_new'(pre) of the layer that produced X
             const uint32_t* p4 = cur.m + 4 * q;
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               const __nv_bfloat162 h = *reinterpret_cast<const __nv_bfloat162*>(&p4[e]);
-              x[2 * e] *= gelu_new_grad(__low2float(h));
-              x[2 * e + 1] *= gelu_new_grad(__high2float(h));
+              x[2 * e] *= __low2float(h);
+              x[2 * e + 1] *= __high2float(h);
             }
           }
-          if (p.act == 1) {
+          if (p.act == 1) {  // gelu_new and its derivative share the tanh
+            float dg[8];
 #pragma unroll
-            for (int e = 0; e < 4; ++e) wp[4 * q + e] = pack_bf16x2(x[2 * e], x[2 * e + 1]);
+            for (int e = 0; e < 8; ++e) gelu_new_both(x[e], x[e], dg[e]);
 #pragma unroll
-            for (int e = 0; e < 8; ++e) x[e] = gelu_new(x[e]);
+            for (int e = 0; e < 4; ++e) wp[4 * q + e] = pack_bf16x2(dg[2 * e], dg[2 * e + 1]);
           }
           if (p.residual != nullptr) {
             const uint32_t* r4 = cur.r + 4 * q;

@@ -1,12 +1,13 @@
-"""Linear layers and MLP of the transformer trunk on the B200 kernels (first pieces).
+"""The transformer trunk on the B200 kernels: linear layers, MLP, attention, LayerNorm, whole blocks.
 
 The reference trains whatever HF causal LM ``--model`` names through ``model(**inputs)`` (FT.py:479) with gradient
 checkpointing on (FT.py:884).  The trunk is third-party code; this module swaps the pieces of it that the existing
 tcgen05 kernel template covers, leaving the module tree, parameter names and checkpoints untouched:
 
   ``linear(x, weight, bias)``                  torch.nn.functional.linear            -> ftk_linear_fwd / ftk_linear_bwd
-  ``mlp_gelu_new(x, w_fc, b_fc, w_proj, b_proj)``   c_proj(gelu_new(c_fc(x)))       -> two GEMMs; bias + GELU live in the first
-                                                one's epilogue, and the GELU's derivative in the epilogue of the second
+  ``mlp_gelu_new(x, w_fc, b_fc, w_proj, b_proj)``   c_proj(gelu_new(c_fc(x)))       -> two GEMMs; bias + GELU (and its saved
+                                                derivative) live in the first one's epilogue, the multiplication by that
+                                                derivative in the epilogue of the second
                                                 one's dX GEMM, so no elementwise kernel ever touches the [tokens, 4d]
                                                 activations
   ``patch_gpt_neo(model)``                     rebinds the forward of every GPTNeoMLP and of the attention projections
@@ -61,7 +62,7 @@ def _check(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor]) -> Tuple
 @torch.library.custom_op("ftk::linear_fwd", mutates_args=())
 def linear_fwd(x: torch.Tensor, w: torch.Tensor, b: Optional[torch.Tensor], residual: Optional[torch.Tensor], act: int,
                save_pre: bool) -> Tuple[torch.Tensor, torch.Tensor]:
-    """(y, pre): y = act(x @ w.T + b) + residual; pre = x @ w.T + b when ``save_pre`` (else empty)."""
+    """(y, dact): y = act(x @ w.T + b) + residual; dact = gelu_new'(x @ w.T + b) when ``save_pre`` (else empty)."""
     global _launches
     M, K, N = _check(x, w, b)
     _check_like(residual, M, N, "residual")
@@ -113,7 +114,8 @@ def _bwd_impl(x, w, dy, mul_pre, dx_add, need_dx, dw_mode, dW_into, need_db):
 def linear_bwd(x: torch.Tensor, w: torch.Tensor, dy: torch.Tensor, mul_pre: Optional[torch.Tensor],
                dx_add: Optional[torch.Tensor], need_dx: bool, need_dw: bool, need_db: bool
                ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor]:
-    """(dx, dw, db) of y = x @ w.T + b; dx is multiplied by gelu_new'(mul_pre) when given, then ``dx_add`` is added.
+    """(dx, dw, db) of y = x @ w.T + b; dx is multiplied by ``mul_pre`` (the saved gelu_new' of the layer that produced
+    x) when given, then ``dx_add`` is added.
     Unwanted ones are empty."""
     return _bwd_impl(x, w, dy, mul_pre, dx_add, need_dx, int(need_dw), None, need_db)
 
@@ -169,18 +171,18 @@ class _Linear(torch.autograd.Function):
 class _MlpGeluNew(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w_fc, b_fc, w_proj, b_proj, residual):
-        a, pre = torch.ops.ftk.linear_fwd(x, w_fc, b_fc, None, ACT_GELU_NEW, True)
+        a, dact = torch.ops.ftk.linear_fwd(x, w_fc, b_fc, None, ACT_GELU_NEW, True)  # dact = gelu_new'(c_fc(x))
         y, _ = torch.ops.ftk.linear_fwd(a, w_proj, b_proj, residual, ACT_NONE, False)
-        ctx.save_for_backward(x, w_fc, b_fc, w_proj, b_proj, pre, a)
+        ctx.save_for_backward(x, w_fc, b_fc, w_proj, b_proj, dact, a)
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        x, w_fc, b_fc, w_proj, b_proj, pre, a = ctx.saved_tensors
+        x, w_fc, b_fc, w_proj, b_proj, dact, a = ctx.saved_tensors
         ng = ctx.needs_input_grad
         dy = dy.contiguous()
-        # c_proj: its dX GEMM hands back d(pre) directly (epilogue multiplies by gelu_new'(pre))
-        dpre, dw_proj, db_proj = _backward(a, w_proj, b_proj, dy, pre, True, ng[3], b_proj is not None and ng[4])
+        # c_proj: its dX GEMM hands back d(pre) directly (its epilogue multiplies by the saved gelu_new'(pre))
+        dpre, dw_proj, db_proj = _backward(a, w_proj, b_proj, dy, dact, True, ng[3], b_proj is not None and ng[4])
         dx, dw_fc, db_fc = _backward(x, w_fc, b_fc, dpre, None, ng[0], ng[1], b_fc is not None and ng[2])
         return dx, dw_fc, db_fc, dw_proj, db_proj, (dy if ng[5] else None)
 
