@@ -326,7 +326,8 @@ int ftk_layernorm_bwd(const void* dY, const void* X, const void* gamma, const fl
  *   lse        fp32 [B * H * T]: natural-log sum-exp of each row's visible scores (+inf for a row that sees no key,
  *              whose output is 0)
  *   workspace  ftk_attention_bwd_workspace bytes, 16-byte aligned (per query and head: lse in log2 units, row sum of dO * O)
- * Requirements: T % 128 == 0, head_dim 64 or 128, 16-byte aligned buffers. Deterministic (no atomics).
+ * Requirements: T % 128 == 0, head_dim 64 or 128, 16-byte aligned inputs, 32-byte aligned O / dQ / dK / dV.
+ * Deterministic (no atomics).
  */
 int ftk_attention_fwd(const void* Q, const void* K, const void* V, const uint8_t* key_mask, int32_t B, int32_t T, int32_t H,
                       int32_t head_dim, int32_t window, float scale, void* O, float* lse, void* stream);

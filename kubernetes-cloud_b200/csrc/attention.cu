@@ -481,11 +481,11 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
       float v[32];
       tmem_ld32(taddr + c * 32, v);
       tmem_ld_wait();
+      uint32_t w[16];
 #pragma unroll
-      for (int q8 = 0; q8 < 4; ++q8)
-        *reinterpret_cast<uint4*>(dst + c * 32 + q8 * 8) =
-            make_uint4(pack2(v[q8 * 8] * inv, v[q8 * 8 + 1] * inv), pack2(v[q8 * 8 + 2] * inv, v[q8 * 8 + 3] * inv),
-                       pack2(v[q8 * 8 + 4] * inv, v[q8 * 8 + 5] * inv), pack2(v[q8 * 8 + 6] * inv, v[q8 * 8 + 7] * inv));
+      for (int e = 0; e < 16; ++e) w[e] = pack2(v[2 * e] * inv, v[2 * e + 1] * inv);
+      st_global_32B(dst + c * 32, w);  // a thread owns a row: 32-byte stores write whole sectors
+      st_global_32B(dst + c * 32 + 16, w + 8);
     }
   }
   tc_fence_before();
@@ -589,11 +589,11 @@ __device__ __forceinline__ void store_acc_row(uint32_t taddr, __nv_bfloat16* dst
     float v[32];
     tmem_ld32(taddr + c * 32, v);
     tmem_ld_wait();
+    uint32_t w[16];
 #pragma unroll
-    for (int q8 = 0; q8 < 4; ++q8)
-      *reinterpret_cast<uint4*>(dst + c * 32 + q8 * 8) =
-          make_uint4(pack2(v[q8 * 8], v[q8 * 8 + 1]), pack2(v[q8 * 8 + 2], v[q8 * 8 + 3]),
-                     pack2(v[q8 * 8 + 4], v[q8 * 8 + 5]), pack2(v[q8 * 8 + 6], v[q8 * 8 + 7]));
+    for (int e = 0; e < 16; ++e) w[e] = pack2(v[2 * e], v[2 * e + 1]);
+    st_global_32B(dst + c * 32, w);  // a thread owns a row: 32-byte stores write whole sectors
+    st_global_32B(dst + c * 32 + 16, w + 8);
   }
 }
 
@@ -1021,6 +1021,7 @@ extern "C" int ftk_attention_fwd(const void* Q, const void* K, const void* V, co
   ftk::DeviceInfo di;
   if (int rc = check_attn(Q, K, V, B, T, H, head_dim, scale, &di)) return rc;
   FTK_REQUIRE(O && lse, "ftk_attention_fwd: null output");
+  FTK_REQUIRE(reinterpret_cast<uintptr_t>(O) % 32 == 0, "ftk_attention_fwd: O must be 32-byte aligned");
   FTK_REQUIRE(window >= 0, "ftk_attention_fwd: negative window");
   AttnParams p = {};
   p.key_mask = key_mask;
@@ -1046,6 +1047,8 @@ extern "C" int ftk_attention_bwd(const void* Q, const void* K, const void* V, co
   ftk::DeviceInfo di;
   if (int rc = check_attn(Q, K, V, B, T, H, head_dim, scale, &di)) return rc;
   FTK_REQUIRE(O && dO && lse && dQ && dK && dV && workspace, "ftk_attention_bwd: null pointer argument");
+  FTK_REQUIRE((reinterpret_cast<uintptr_t>(dQ) | reinterpret_cast<uintptr_t>(dK) | reinterpret_cast<uintptr_t>(dV)) % 32 == 0,
+              "ftk_attention_bwd: dQ, dK and dV must be 32-byte aligned");
   FTK_REQUIRE(window >= 0, "ftk_attention_bwd: negative window");
   if (workspace_bytes < ftk_attention_bwd_workspace(B, T, H))
     return ftk::fail(FTK_EWORKSPACE, "ftk_attention_bwd: workspace %zu bytes < required %zu", workspace_bytes,

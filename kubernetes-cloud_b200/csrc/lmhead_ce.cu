@@ -411,19 +411,6 @@ struct FwdKeepEpi {
 // store instruction touches 32 different rows: with 16-byte accesses every one of them is half a 32-byte sector and the
 // L2 has to merge two partial writes per sector (the c_fc GEMM that also stores its pre-activation ran at 868 TF/s
 // with 16-byte stores and at 1326 TF/s, the speed of the plain GEMM, with 32-byte ones).
-__device__ __forceinline__ void st_global_32B(void* p, const uint32_t w[8]) {
-  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]),
-               "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
-               : "memory");
-}
-
-__device__ __forceinline__ void ld_global_32B(const void* p, uint32_t w[8]) {
-  asm volatile("ld.global.v8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-               : "=r"(w[0]), "=r"(w[1]), "=r"(w[2]), "=r"(w[3]), "=r"(w[4]), "=r"(w[5]), "=r"(w[6]), "=r"(w[7])
-               : "l"(p)
-               : "memory");
-}
-
 // Plain GEMM epilogue: out[row, col] (+)= acc, bf16 or fp32 row-major.  Under split-K each split writes its partial
 // sums to its own copy of the output, split_stride elements apart (summed afterwards in a fixed order).
 template <bool kF32>
