@@ -499,21 +499,22 @@ __global__ void __launch_bounds__(kAttnThreads, 1)
 // ------------------------------------------------------------------------------------------------ backward
 // stats[b, h, t] = (lse * log2(e), scale * delta) with delta = sum_c dO[row, h * DH + c] * O[row, h * DH + c]: what the
 // two backward kernels need per query (dS = P * (scale * dP - scale * delta)), packed so that one 512-byte bulk copy
-// brings a sub-tile's 64 pairs.  One thread per (row, head).
+// brings a sub-tile's 64 pairs.
 template <int DH>
 __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __restrict__ o,
                                                          const __nv_bfloat16* __restrict__ d_o,
                                                          const float* __restrict__ lse, float2* __restrict__ stats,
                                                          int n_rows, int T, int H, float scale) {
-  const int idx = blockIdx.x * 256 + threadIdx.x;
-  if (idx >= n_rows * H) return;
-  const int row = idx / H, h = idx - row * H;
-  const uint4* a = reinterpret_cast<const uint4*>(o + static_cast<size_t>(row) * H * DH + h * DH);
-  const uint4* b = reinterpret_cast<const uint4*>(d_o + static_cast<size_t>(row) * H * DH + h * DH);
+  // DH / 8 lanes share one (row, head): a warp reads 512 contiguous bytes of O and of dO per instruction
+  constexpr int kLanes = DH / 8, kItems = 32 / kLanes;
+  const int lane = threadIdx.x & 31, sub = lane % kLanes;
+  const int64_t warp_id = (static_cast<int64_t>(blockIdx.x) * 256 + threadIdx.x) >> 5;
+  const int64_t idx = warp_id * kItems + lane / kLanes;  // (row, head) pairs are consecutive in memory: row * H + head
+  const bool live = idx < static_cast<int64_t>(n_rows) * H;
   float acc = 0.f;
-#pragma unroll
-  for (int i = 0; i < DH / 8; ++i) {
-    const uint4 x = a[i], y = b[i];
+  if (live) {
+    const uint4 x = __ldg(reinterpret_cast<const uint4*>(o + idx * DH) + sub);
+    const uint4 y = __ldg(reinterpret_cast<const uint4*>(d_o + idx * DH) + sub);
     const uint32_t xw[4] = {x.x, x.y, x.z, x.w}, yw[4] = {y.x, y.y, y.z, y.w};
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
@@ -522,9 +523,14 @@ __global__ void __launch_bounds__(256) attn_delta_kernel(const __nv_bfloat16* __
       acc += __low2float(xh) * __low2float(yh) + __high2float(xh) * __high2float(yh);
     }
   }
-  const int bb = row / T, t = row - bb * T;
-  const size_t i = (static_cast<size_t>(bb) * H + h) * T + t;
-  stats[i] = make_float2(lse[i] * kLog2e, acc * scale);  // lse = +inf for a row that saw no key: every p is 0
+#pragma unroll
+  for (int off = kLanes / 2; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+  if (live && sub == 0) {
+    const int row = static_cast<int>(idx / H), h = static_cast<int>(idx - static_cast<int64_t>(row) * H);
+    const int bb = row / T, t = row - bb * T;
+    const size_t i = (static_cast<size_t>(bb) * H + h) * T + t;
+    stats[i] = make_float2(lse[i] * kLog2e, acc * scale);  // lse = +inf for a row that saw no key: every p is 0
+  }
 }
 
 // The backward kernels work on 64-wide sub-tiles of the streamed operand so that everything can be double-buffered
@@ -995,8 +1001,8 @@ int run_attn_bwd(const void* q, const void* k, const void* v, const void* o, con
   if (int rc = set_smem(attn_bwd_kv_kernel<DH>, BwdKvSmem<DH>::BYTES)) return rc;
   if (int rc = set_smem(attn_bwd_q_kernel<DH>, BwdQSmem<DH>::BYTES)) return rc;
   ftk::TimelineScope tl_(FTK_TL_ATTN_BWD, st);
-  const int n = B * p.T * p.H;
-  attn_delta_kernel<DH><<<(n + 255) / 256, 256, 0, st>>>(static_cast<const __nv_bfloat16*>(o),
+  const int64_t n = static_cast<int64_t>(B) * p.T * p.H * (DH / 8);  // threads: DH / 8 lanes per (row, head)
+  attn_delta_kernel<DH><<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(static_cast<const __nv_bfloat16*>(o),
                                                         static_cast<const __nv_bfloat16*>(d_o), p.lse, stats, B * p.T, p.T,
                                                         p.H, p.scale);
   FTK_CUDA_CHECK(cudaGetLastError());
