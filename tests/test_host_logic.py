@@ -334,3 +334,16 @@ def test_fused_slab_planner():
                 assert r % 256 == 0 and 2816 <= r <= M
                 assert r * ((V + 63) // 64 * 64) * 2 <= 1 << 30
     assert L.ftk_lmhead_ce_fused_plan(0, 2048, 50257, 148, 2) == 0 and L.ftk_lmhead_ce_fused_plan(4096, 2048, 50257, 148, 3) == 0
+
+
+def test_recompute_flag_parses():
+    """--ftk-recompute: this command line's own switch for the reference's always-on gradient checkpointing (FT.py:884,
+    :995): auto (default) / on / off; anything else is an argparse error (exit code 2 as for the reference's flags)."""
+    from kubernetes_cloud_b200.finetune import build_parser
+    base = ["--run-name", "r", "--model", "gpt-neo-125m", "--dataset", __file__]
+    assert build_parser().parse_args(base).ftk_recompute == "auto"
+    for v in ("on", "off", "auto"):
+        assert build_parser().parse_args(base + [f"--ftk-recompute={v}"]).ftk_recompute == v
+    with pytest.raises(SystemExit) as e:
+        build_parser().parse_args(base + ["--ftk-recompute=maybe"])
+    assert e.value.code == 2
