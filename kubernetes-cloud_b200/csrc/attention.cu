@@ -20,10 +20,10 @@
 // tensor work); what mattered was removing the fp32 score tensors.
 //
 // Every mbarrier wait here is a pure poll (mbarrier.test_wait): the suspending form (try_wait + NANOSLEEP.SYNCS) wakes
-// up late enough to stall these pipelines on their single issuing thread.
+// up late enough to stall these pipelines on their issuing warps.
 //
-// One warp (lane 0) issues TMA and MMA; eight warps own the accumulator rows, two threads per row (softmax, tile
-// conversion).  All three kernels are software pipelines: S (and dP) have two TMEM buffers, so the tensor pipe forms
+// Two warps issue TMA and MMA (an elected lane each); eight warps own the accumulator rows, two threads per row
+// (softmax, tile conversion).  All three kernels are software pipelines: S (and dP) have two TMEM buffers, so the tensor pipe forms
 // the scores of tile t+1 while the row threads work on tile t and applies tile t's P / dS to the accumulators while
 // they work on tile t+1; operands arrive through multi-stage TMA rings.  A tile that lies wholly inside the causal /
 // window band and holds no padding skips every per-element test; the others use one visibility bit mask per row.
