@@ -159,6 +159,10 @@ def build_parser() -> DashParser:
                    help="gradient checkpointing (FT.py:884, :995: always on in the reference, sized for 48 GB cards). "
                         "'off' keeps every block's activations for the backward instead of re-running its forward; "
                         "'auto' does so when they fit in half of the free device memory (180 GB of HBM usually do)")
+    p.add_argument("--ftk-sm-reserve", type=_number(int, low=0, high=64), default=0,
+                   help="data parallel only: SMs the persistent GEMM kernels leave idle so that the gradient "
+                        "all-reduce's NCCL kernels find room beside them (their CTAs cannot share an SM with a GEMM "
+                        "CTA that holds the whole register file); 0 = the all-reduce runs in the gaps between kernels")
     p.add_argument("--no-ftk-trunk", action=FuzzyBool, dest="ftk_trunk", default=True,
                    help="keep HF's eager GPT-Neo blocks; by default their MLP, projections and attention run on this "
                         "package's kernels (trunk.patch_gpt_neo) when the context size is a multiple of 128")
@@ -278,6 +282,9 @@ def main(argv: Optional[List[str]] = None) -> dict:
     total_steps = steps_per_epoch * args.epochs
     if args.max_steps > 0:
         total_steps = min(total_steps, args.max_steps)
+    if world > 1 and args.ftk_sm_reserve > 0:
+        from . import _lib
+        _lib.set_option("sm_reserve", args.ftk_sm_reserve)
     sync = GradSync(model.parameters(), rank, world)
     opt = FusedAdamW(sync, lr=args.lr, weight_decay=0.01, max_grad_norm=args.max_grad_norm,
                      schedule=WarmupLR(args.lr, max(2, int(float(args.warmup_ratio) * total_steps))))
