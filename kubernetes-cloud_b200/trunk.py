@@ -458,8 +458,8 @@ def _block_forward(self, hidden_states, layer_past=None, attention_mask=None, us
     only: LayerNorm forks, chained q/k/v projections, attention, and the two residual adds inside the epilogues of
     out_proj's and c_proj's GEMMs.  Same parameters, same result up to bf16 rounding (the adds happen in fp32 before
     the single rounding); no elementwise kernel runs, forward or backward."""
-    if layer_past is not None or use_cache or output_attentions:
-        raise _lib.FtkError("the fused block serves training steps only (no KV cache, no attention maps)")
+    if layer_past is not None or use_cache or output_attentions or kwargs.get("head_mask") is not None:
+        raise _lib.FtkError("the fused block serves training steps only (no KV cache, no attention maps, no head mask)")
     B, T, D = hidden_states.shape
     att = self.attn.attention
     x = hidden_states.reshape(B * T, D)
@@ -536,8 +536,9 @@ def patch_gpt_neo(model, attention_kernels: Optional[bool] = None, fuse_blocks: 
 
             def attn_forward(self, hidden_states, attention_mask=None, layer_past=None, use_cache=False,
                              output_attentions=False, _window=window, **kwargs):
-                if layer_past is not None or use_cache or output_attentions:
-                    raise _lib.FtkError("the fused attention serves training steps only (no KV cache, no attention maps)")
+                if layer_past is not None or use_cache or output_attentions or kwargs.get("head_mask") is not None:
+                    raise _lib.FtkError("the fused attention serves training steps only (no KV cache, no attention maps, "
+                                        "no head mask)")
                 q, k, v = qkv(hidden_states, self.q_proj.weight, self.q_proj.bias, self.k_proj.weight, self.k_proj.bias,
                               self.v_proj.weight, self.v_proj.bias)
                 o = attention(q, k, v, _key_mask_of(attention_mask), self.num_heads, _window, 1.0)  # GPT-Neo: no scale
