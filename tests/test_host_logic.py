@@ -347,3 +347,44 @@ def test_recompute_flag_parses():
     with pytest.raises(SystemExit) as e:
         build_parser().parse_args(base + ["--ftk-recompute=maybe"])
     assert e.value.code == 2
+
+
+def test_patch_gpt_neo_host_side_rules():
+    """trunk.patch_gpt_neo only rebinds forwards (no kernel runs): which modules it takes over for which configuration,
+    and what it refuses -- a model it does not know, dropout (the fused blocks have none), whole-block fusion without
+    the attention kernels or with a hidden size the LayerNorm kernels do not take."""
+    from transformers import GPT2Config, GPT2LMHeadModel, GPTNeoConfig, GPTNeoForCausalLM
+    from kubernetes_cloud_b200 import FtkError, trunk
+
+    def neo(**kw):
+        cfg = dict(vocab_size=128, hidden_size=256, num_layers=2, num_heads=4, max_position_embeddings=128,
+                   attention_types=[[["global", "local"], 1]], window_size=32)
+        cfg.update(kw)
+        return GPTNeoForCausalLM(GPTNeoConfig(**cfg))
+
+    m = neo()                                        # head_dim 64, hidden 256: everything, whole blocks fused
+    assert trunk.patch_gpt_neo(m) == 2 * 9 + 1 and m.config.use_cache is False
+    assert trunk.patch_gpt_neo(neo(), fuse_blocks=False) == 2 * 6
+    assert trunk.patch_gpt_neo(neo(hidden_size=128, num_heads=2)) == 2 * 6       # LayerNorm kernels need hidden % 256 == 0
+    assert trunk.patch_gpt_neo(neo(hidden_size=256, num_heads=8)) == 2 * 5       # head_dim 32: HF's attention stays
+    with pytest.raises(FtkError):
+        trunk.patch_gpt_neo(neo(hidden_size=256, num_heads=8), attention_kernels=True)
+    with pytest.raises(FtkError):
+        trunk.patch_gpt_neo(neo(hidden_size=128, num_heads=2), fuse_blocks=True)
+    with pytest.raises(FtkError):
+        trunk.patch_gpt_neo(neo(resid_dropout=0.1))
+    with pytest.raises(FtkError):
+        trunk.patch_gpt_neo(neo(attention_dropout=0.1))
+    with pytest.raises(FtkError):
+        trunk.patch_gpt_neo(neo(activation_function="gelu"))
+    with pytest.raises(FtkError):
+        trunk.patch_gpt_neo(GPT2LMHeadModel(GPT2Config(vocab_size=128, n_embd=64, n_layer=1, n_head=2, n_positions=64)))
+    # the rebound modules refuse what they do not implement instead of ignoring it (CPU tensors never reach a kernel)
+    blk = m.base_model.h[0]
+    x = torch.zeros(1, 128, 256)
+    with pytest.raises(FtkError):
+        blk(x, use_cache=True)
+    with pytest.raises(FtkError):
+        blk(x, head_mask=torch.ones(4))
+    with pytest.raises(FtkError):
+        blk(x)                                       # CPU tensors: no fallback
